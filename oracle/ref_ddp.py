@@ -1,0 +1,193 @@
+"""CPU restatement of the reference's manual data-parallel step.
+
+TEST INFRASTRUCTURE ONLY (see oracle/__init__.py).  Every function cites the
+reference lines it follows; `oracle/make_golden.py` checks each one against
+the reference function imported from /root/reference and freezes the outputs
+under tests/golden/.
+
+The arithmetic itself lives in third-party torch (c10d all_reduce, ATen div_,
+torch.optim.SGD); the reference pins torch 1.13.1
+(codes/task2/docker-compose.yml:6), this image has 2.11.0 - the semantics used
+here are unchanged between the two.
+"""
+from __future__ import annotations
+
+import os
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.nn as nn
+import torch.nn.functional as F
+
+
+# --------------------------------------------------------------------------
+# process group helpers: codes/task4/dist_utils.py:6-30 (the gloo twin of
+# codes/task2/dist_utils.py:6-30, which hard-codes "nccl")
+# --------------------------------------------------------------------------
+def dist_init(world_size, rank, master_addr="127.0.0.1", master_port="12355",
+              backend="gloo"):
+    os.environ["MASTER_ADDR"] = str(master_addr)
+    os.environ["MASTER_PORT"] = str(master_port)
+    dist.init_process_group(backend=backend, rank=rank, world_size=world_size)
+    assert dist.is_initialized()
+    return True
+
+
+def get_local_rank():
+    # codes/task2/dist_utils.py:18-23 - returns the *global* rank.
+    return dist.get_rank() if dist.is_initialized() else 0
+
+
+def get_world_size():
+    # codes/task2/dist_utils.py:26-30
+    return dist.get_world_size() if dist.is_initialized() else 1
+
+
+def init_parameters(model):
+    # codes/task2/dist_utils.py:33-37: parameters only, buffers are not sent.
+    if get_world_size() > 1:
+        for param in model.parameters():
+            dist.broadcast(param.data, 0)
+
+
+def allreduce_average_gradients(model):
+    # codes/task2/dist_utils.py:39-42: one SUM all-reduce per parameter, then
+    # an in-place true division by the (int) world size.
+    for param in model.parameters():
+        dist.all_reduce(param.grad.data, op=dist.ReduceOp.SUM)
+        param.grad.data /= get_world_size()
+
+
+def average_gradients(model):
+    # codes/task3/dist_utils.py:40-46: same, divisor spelled float(size).
+    size = float(get_world_size())
+    for param in model.parameters():
+        dist.all_reduce(param.grad.data, op=dist.ReduceOp.SUM)
+        param.grad.data /= size
+
+
+# --------------------------------------------------------------------------
+# in-process stand-in for the collective, for tests that cannot spawn:
+# sum the ranks' tensors left to right (rank 0 first), then divide.
+# Exact for N <= 2 (fp32 addition is commutative, there is one addition);
+# for N > 2 gloo's order may differ, so callers use the stated tolerance.
+# --------------------------------------------------------------------------
+def average_over_ranks(per_rank: list[torch.Tensor]) -> torch.Tensor:
+    acc = per_rank[0].clone()
+    for t in per_rank[1:]:
+        acc += t
+    acc /= len(per_rank)
+    return acc
+
+
+def bf16_wire_average(per_rank: list[torch.Tensor]) -> torch.Tensor:
+    """torch bf16_compress_hook semantics
+    (torch/distributed/algorithms/ddp_comm_hooks/default_hooks.py:57-93):
+    cast to bf16, divide by N, sum in bf16, cast back to fp32."""
+    n = len(per_rank)
+    acc = per_rank[0].to(torch.bfloat16).div_(n)
+    for t in per_rank[1:]:
+        acc += t.to(torch.bfloat16).div_(n)
+    return acc.to(torch.float32)
+
+
+# --------------------------------------------------------------------------
+# momentum SGD, restating torch/optim/sgd.py:322-380 (_single_tensor_sgd),
+# which is what optimizer.step() at codes/task2/model.py:62 runs.
+# add_(x, alpha=a) on CPU is a fused multiply-add (checked in make_golden.py),
+# emulated here through float64 (product of two fp32 is exact in fp64).
+# --------------------------------------------------------------------------
+def _fma32(a, b, c):
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64)
+            + np.asarray(c, np.float64)).astype(np.float32)
+
+
+def sgd_step_numpy(p, g, buf, *, lr, momentum=0.0, dampening=0.0,
+                   weight_decay=0.0, nesterov=False, maximize=False):
+    """Returns (new_p, new_buf).  `buf is None` means first step."""
+    p = np.asarray(p, np.float32)
+    g = np.asarray(g, np.float32)
+    if maximize:
+        g = -g
+    if weight_decay != 0:
+        g = _fma32(np.float32(weight_decay), p, g)           # sgd.py:346-356
+    if momentum != 0:
+        if buf is None:
+            buf = g.copy()                                    # sgd.py:361-363
+        else:
+            buf = (np.asarray(buf, np.float32) * np.float32(momentum)).astype(np.float32)
+            buf = _fma32(np.float32(1 - dampening), g, buf)   # sgd.py:365
+        g = _fma32(np.float32(momentum), buf, g) if nesterov else buf  # :367-370
+    new_p = _fma32(np.float32(-lr), g, p)                     # sgd.py:380
+    return new_p, buf
+
+
+# --------------------------------------------------------------------------
+# the lab CNN: same layers, shapes and parameter order as `Net` at
+# codes/task2/model.py:13-37 (51,902 parameters in 8 tensors).
+# --------------------------------------------------------------------------
+class LabNet(nn.Module):
+    def __init__(self, in_channels=1, num_classes=10):
+        super().__init__()
+        self.conv1 = nn.Conv2d(in_channels, 6, 5, stride=1, padding=2)
+        self.conv2 = nn.Conv2d(6, 16, 5, stride=1, padding=0)
+        self.fc1 = nn.Linear(16 * 5 * 5, 120)
+        self.fc2 = nn.Linear(120, num_classes)
+
+    def forward(self, x):
+        x = F.max_pool2d(F.relu(self.conv1(x)), 2)
+        x = F.max_pool2d(F.relu(self.conv2(x)), 2)
+        x = F.relu(self.fc1(x.flatten(1)))
+        return self.fc2(x)
+
+
+LABNET_NUMELS = (150, 6, 2400, 16, 48000, 120, 1200, 10)
+
+
+def synthetic_batch(rank, step, batch, chw, classes):
+    """Per-rank synthetic batch: ToTensor-range images
+    and integer labels from a generator seeded 1234 + rank, advanced `step`
+    batches."""
+    g = torch.Generator().manual_seed(1234 + rank)
+    for _ in range(step + 1):
+        x = torch.rand((batch,) + tuple(chw), generator=g)
+        y = torch.randint(0, classes, (batch,), generator=g)
+    return x, y
+
+
+def build_model(name):
+    """Models of BASELINE.json's configs, constructed after manual_seed(0) so
+    that buffers agree across ranks."""
+    torch.manual_seed(0)
+    if name == "labnet":
+        return LabNet(1, 10), (1, 28, 28), 10
+    import torchvision
+    if name == "resnet18":
+        return torchvision.models.resnet18(num_classes=10), (3, 32, 32), 10
+    if name == "resnet50":
+        return torchvision.models.resnet50(), (3, 224, 224), 1000
+    raise ValueError(name)
+
+
+def train_steps(model, rank, steps, batch, chw, classes, lr=0.01, momentum=0.9,
+                sync=allreduce_average_gradients, record=None):
+    """The hot loop of codes/task2/model.py:49-63 on synthetic batches.
+    `record(step, local_grads, avg_grads)` is called after the sync."""
+    opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=momentum)
+    loss_fn = nn.CrossEntropyLoss()
+    model.train()
+    init_parameters(model)
+    losses = []
+    for s in range(steps):
+        x, y = synthetic_batch(rank, s, batch, chw, classes)
+        loss = loss_fn(model(x), y)
+        opt.zero_grad()
+        loss.backward()
+        local = [p.grad.detach().clone() for p in model.parameters()] if record else None
+        sync(model)
+        if record:
+            record(s, local, [p.grad.detach().clone() for p in model.parameters()])
+        opt.step()
+        losses.append(float(loss))
+    return opt, losses
