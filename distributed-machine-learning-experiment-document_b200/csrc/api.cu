@@ -1,0 +1,539 @@
+// extern "C" surface of libb200ddp.so: contexts, plans, argument checking and
+// dispatch.  Declarations and the reference lines each entry point replaces
+// are in include/b200ddp.h.
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <cmath>
+#include <new>
+
+#include "internal.h"
+
+namespace b200ddp {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+static size_t dtype_size(int dtype) { return dtype == B200DDP_BF16 ? 2 : 4; }
+
+PlanView plan_view(const b200ddp_plan *plan) {
+    PlanView pv;
+    pv.meta = plan->d_meta;
+    pv.chunks = plan->d_chunks;
+    pv.nchunks = (int)plan->chunks.size();
+    pv.T = plan->T;
+    for (int k = 0; k < kNumPtrKinds; ++k) pv.ptrs[k] = plan->d_ptrs + (size_t)k * plan->T;
+    return pv;
+}
+
+// Device pointer tables are refreshed only when a pointer changed (p.grad is
+// re-allocated by autograd every step; params and momentum never move).
+int plan_upload(b200ddp_plan *plan, PtrKind kind, const void *const *host_ptrs, cudaStream_t s) {
+    const int T = plan->T;
+    if (T == 0) return B200DDP_OK;
+    B2_REQUIRE(host_ptrs != nullptr, B200DDP_EINVAL, "pointer table %d is NULL", (int)kind);
+    for (int t = 0; t < T; ++t)
+        B2_REQUIRE(host_ptrs[t] != nullptr || plan->meta[t].numel == 0, B200DDP_EINVAL,
+                   "tensor %d of pointer table %d is NULL", t, (int)kind);
+    void **mirror = plan->h_ptrs.data() + (size_t)kind * T;
+    if (plan->uploaded[kind] && memcmp(mirror, host_ptrs, sizeof(void *) * T) == 0) return B200DDP_OK;
+    const int slot = plan->ring_pos;
+    plan->ring_pos = (slot + 1) % b200ddp_plan::kRing;
+    B2_CHECK_CUDA(cudaEventSynchronize(plan->pinned_ev[slot]));   // slot free again (no-op if never recorded)
+    memcpy(plan->pinned[slot], host_ptrs, sizeof(void *) * T);
+    B2_CHECK_CUDA(cudaMemcpyAsync(plan->d_ptrs + (size_t)kind * T, plan->pinned[slot], sizeof(void *) * T,
+                                  cudaMemcpyHostToDevice, s));
+    B2_CHECK_CUDA(cudaEventRecord(plan->pinned_ev[slot], s));
+    memcpy(mirror, host_ptrs, sizeof(void *) * T);
+    plan->uploaded[kind] = true;
+    return B200DDP_OK;
+}
+
+int sgd_scalars(const b200ddp_sgd_args *a, SgdScalars *o) {
+    B2_REQUIRE(a != nullptr, B200DDP_EINVAL, "sgd args is NULL");
+    B2_REQUIRE(std::isfinite(a->lr) && std::isfinite(a->momentum) && std::isfinite(a->dampening) &&
+                   std::isfinite(a->weight_decay) && std::isfinite(a->grad_divisor),
+               B200DDP_EINVAL, "non-finite SGD hyper-parameter");
+    B2_REQUIRE(a->grad_divisor != 0.0, B200DDP_EINVAL, "grad_divisor must not be 0");
+    B2_REQUIRE(!a->nesterov || (a->momentum > 0 && a->dampening == 0), B200DDP_EINVAL,
+               "Nesterov momentum requires a momentum and zero dampening");
+    o->neg_lr = (float)(-a->lr);
+    o->momentum = (float)a->momentum;
+    o->one_minus_damp = (float)(1.0 - a->dampening);
+    o->weight_decay = (float)a->weight_decay;
+    o->divisor = (float)a->grad_divisor;
+    o->use_div = a->grad_divisor != 1.0;
+    o->nesterov = a->nesterov != 0;
+    o->maximize = a->maximize != 0;
+    o->first_step = a->first_step != 0;
+    o->has_momentum = a->momentum != 0.0;
+    o->has_wd = a->weight_decay != 0.0;
+    return B200DDP_OK;
+}
+
+static int check_plan(b200ddp_ctx *ctx, b200ddp_plan *plan) {
+    B2_REQUIRE(ctx != nullptr && plan != nullptr, B200DDP_EINVAL, "ctx or plan is NULL");
+    B2_REQUIRE(plan->ctx == ctx, B200DDP_EINVAL, "plan belongs to another context");
+    return B200DDP_OK;
+}
+
+static int in_staging(const b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype) {
+    B2_REQUIRE(dtype == B200DDP_F32 || dtype == B200DDP_BF16, B200DDP_EINVAL, "bad dtype %d", dtype);
+    B2_REQUIRE(nelem >= 0, B200DDP_EINVAL, "negative element count");
+    B2_REQUIRE(off % 256 == 0, B200DDP_EINVAL, "bucket offset %zu is not 256-byte aligned", off);
+    B2_REQUIRE((nelem * (int64_t)dtype_size(dtype)) % 16 == 0, B200DDP_EINVAL,
+               "bucket of %lld elements is not a whole number of 16-byte vectors", (long long)nelem);
+    B2_REQUIRE(off + (size_t)nelem * dtype_size(dtype) <= ctx->staging_bytes, B200DDP_ETOOBIG,
+               "bucket [%zu, +%lld x %zu B) exceeds the %zu-byte staging area", off, (long long)nelem,
+               dtype_size(dtype), ctx->staging_bytes);
+    return B200DDP_OK;
+}
+
+}  // namespace b200ddp
+
+using namespace b200ddp;
+
+extern "C" {
+
+const char *b200ddp_last_error(void) { return g_err; }
+int b200ddp_version(void) { return 100; }
+
+int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200ddp_ctx **out) {
+    B2_REQUIRE(out != nullptr, B200DDP_EINVAL, "out is NULL");
+    *out = nullptr;
+    B2_REQUIRE(world >= 1 && world <= B200DDP_MAX_WORLD, B200DDP_EINVAL, "world size %d not in [1, %d]", world,
+               B200DDP_MAX_WORLD);
+    B2_REQUIRE(rank >= 0 && rank < world, B200DDP_EINVAL, "rank %d not in [0, %d)", rank, world);
+    int ndev = 0;
+    B2_CHECK_CUDA(cudaGetDeviceCount(&ndev));
+    B2_REQUIRE(device >= 0 && device < ndev, B200DDP_EINVAL, "device %d not in [0, %d)", device, ndev);
+    B2_CHECK_CUDA(cudaSetDevice(device));
+    b200ddp_ctx *ctx = new (std::nothrow) b200ddp_ctx();
+    B2_REQUIRE(ctx != nullptr, B200DDP_ESTATE, "out of host memory");
+    ctx->rank = rank;
+    ctx->world = world;
+    ctx->device = device;
+    ctx->staging_bytes = (staging_bytes + 255) / 256 * 256;
+    int sms = 0;
+    if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0)
+        ctx->sm_count = sms;
+    const size_t flag_bytes = sizeof(uint32_t) * kMaxBlocksP2P * B200DDP_MAX_WORLD;
+    cudaError_t e = cudaMalloc((void **)&ctx->staging, 2 * ctx->staging_bytes + 256);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->flags, flag_bytes);
+    if (e == cudaSuccess) e = cudaMemset(ctx->staging, 0, 2 * ctx->staging_bytes + 256);
+    if (e == cudaSuccess) e = cudaMemset(ctx->flags, 0, flag_bytes);
+    if (e == cudaSuccess) e = cudaDeviceSynchronize();
+    if (e != cudaSuccess) {
+        set_error("allocating %zu bytes of staging on device %d failed: %s", 2 * ctx->staging_bytes, device,
+                  cudaGetErrorString(e));
+        cudaFree(ctx->staging);
+        cudaFree(ctx->flags);
+        delete ctx;
+        return B200DDP_ECUDA;
+    }
+    for (int r = 0; r < B200DDP_MAX_WORLD; ++r) {
+        ctx->peers.staging[r] = nullptr;
+        ctx->peers.flags[r] = nullptr;
+    }
+    ctx->peers.staging[rank] = ctx->staging;
+    ctx->peers.flags[rank] = ctx->flags;
+    ctx->peers_ready = (world == 1);
+    *out = ctx;
+    return B200DDP_OK;
+}
+
+int b200ddp_destroy(b200ddp_ctx *ctx) {
+    if (!ctx) return B200DDP_OK;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    nccl_destroy(ctx);
+    if (ctx->peers_ipc) {
+        for (int r = 0; r < ctx->world; ++r) {
+            if (r == ctx->rank) continue;
+            if (ctx->peers.staging[r]) cudaIpcCloseMemHandle(ctx->peers.staging[r]);
+            if (ctx->peers.flags[r]) cudaIpcCloseMemHandle(ctx->peers.flags[r]);
+        }
+    }
+    cudaFree(ctx->sampler_scratch);
+    cudaFree(ctx->staging);
+    cudaFree(ctx->flags);
+    delete ctx;
+    return B200DDP_OK;
+}
+
+int b200ddp_staging(b200ddp_ctx *ctx, void **ptr, size_t *bytes) {
+    B2_REQUIRE(ctx != nullptr, B200DDP_EINVAL, "ctx is NULL");
+    if (ptr) *ptr = ctx->staging;
+    if (bytes) *bytes = ctx->staging_bytes;
+    return B200DDP_OK;
+}
+
+int b200ddp_flags(b200ddp_ctx *ctx, void **ptr) {
+    B2_REQUIRE(ctx != nullptr && ptr != nullptr, B200DDP_EINVAL, "NULL argument");
+    *ptr = ctx->flags;
+    return B200DDP_OK;
+}
+
+int b200ddp_nccl_unique_id(void *out_uid) {
+    B2_REQUIRE(out_uid != nullptr, B200DDP_EINVAL, "out is NULL");
+    return nccl_unique_id(out_uid);
+}
+
+int b200ddp_nccl_init(b200ddp_ctx *ctx, const void *uid) {
+    B2_REQUIRE(ctx != nullptr && uid != nullptr, B200DDP_EINVAL, "NULL argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    return nccl_init(ctx, uid);
+}
+
+int b200ddp_ipc_export(b200ddp_ctx *ctx, void *out) {
+    B2_REQUIRE(ctx != nullptr && out != nullptr, B200DDP_EINVAL, "NULL argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    cudaIpcMemHandle_t h[2];
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    B2_CHECK_CUDA(cudaIpcGetMemHandle(&h[0], ctx->staging));
+    B2_CHECK_CUDA(cudaIpcGetMemHandle(&h[1], ctx->flags));
+    memcpy(out, h, sizeof(h));
+    return B200DDP_OK;
+}
+
+int b200ddp_ipc_open_peers(b200ddp_ctx *ctx, const void *handles) {
+    B2_REQUIRE(ctx != nullptr && handles != nullptr, B200DDP_EINVAL, "NULL argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    B2_REQUIRE(!ctx->peers_ready || ctx->world == 1, B200DDP_ESTATE, "peers already set");
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    const char *hp = (const char *)handles;
+    for (int r = 0; r < ctx->world; ++r) {
+        if (r == ctx->rank) continue;
+        cudaIpcMemHandle_t h[2];
+        memcpy(h, hp + (size_t)r * B200DDP_IPC_BYTES, sizeof(h));
+        void *ps = nullptr, *pf = nullptr;
+        B2_CHECK_CUDA(cudaIpcOpenMemHandle(&ps, h[0], cudaIpcMemLazyEnablePeerAccess));
+        B2_CHECK_CUDA(cudaIpcOpenMemHandle(&pf, h[1], cudaIpcMemLazyEnablePeerAccess));
+        ctx->peers.staging[r] = (char *)ps;
+        ctx->peers.flags[r] = (uint32_t *)pf;
+    }
+    ctx->peers_ipc = true;
+    ctx->peers_ready = true;
+    return B200DDP_OK;
+}
+
+int b200ddp_set_peers_direct(b200ddp_ctx *ctx, void *const *staging_ptrs, void *const *flag_ptrs) {
+    B2_REQUIRE(ctx != nullptr && staging_ptrs != nullptr && flag_ptrs != nullptr, B200DDP_EINVAL, "NULL argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    for (int r = 0; r < ctx->world; ++r) {
+        B2_REQUIRE(staging_ptrs[r] != nullptr && flag_ptrs[r] != nullptr, B200DDP_EINVAL, "peer %d pointer is NULL", r);
+        if (r == ctx->rank) {
+            B2_REQUIRE(staging_ptrs[r] == ctx->staging && flag_ptrs[r] == ctx->flags, B200DDP_EINVAL,
+                       "entry %d must be this context's own staging and flags", r);
+            continue;
+        }
+        cudaPointerAttributes at;
+        B2_CHECK_CUDA(cudaPointerGetAttributes(&at, staging_ptrs[r]));
+        if (at.device != ctx->device) {
+            cudaError_t e = cudaDeviceEnablePeerAccess(at.device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) {
+                cudaGetLastError();
+            } else if (e != cudaSuccess) {
+                set_error("cudaDeviceEnablePeerAccess(%d -> %d) failed: %s", ctx->device, at.device,
+                          cudaGetErrorString(e));
+                return B200DDP_ECUDA;
+            }
+        }
+        ctx->peers.staging[r] = (char *)staging_ptrs[r];
+        ctx->peers.flags[r] = (uint32_t *)flag_ptrs[r];
+    }
+    ctx->peers_ready = true;
+    return B200DDP_OK;
+}
+
+// ---------------------------------------------------------------------- plan
+int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int bucket_dtype, b200ddp_plan **out) {
+    B2_REQUIRE(ctx != nullptr && out != nullptr, B200DDP_EINVAL, "NULL argument");
+    *out = nullptr;
+    B2_REQUIRE(T >= 0 && (T == 0 || numels != nullptr), B200DDP_EINVAL, "bad tensor list");
+    B2_REQUIRE(bucket_dtype == B200DDP_F32 || bucket_dtype == B200DDP_BF16, B200DDP_EINVAL, "bad dtype %d",
+               bucket_dtype);
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    b200ddp_plan *p = new (std::nothrow) b200ddp_plan();
+    B2_REQUIRE(p != nullptr, B200DDP_ESTATE, "out of host memory");
+    p->ctx = ctx;
+    p->T = T;
+    p->dtype = bucket_dtype;
+    int64_t off = 0;
+    for (int t = 0; t < T; ++t) {
+        if (numels[t] < 0) {
+            set_error("tensor %d has negative numel", t);
+            delete p;
+            return B200DDP_EINVAL;
+        }
+        p->meta.push_back({numels[t], off});
+        const int64_t nch = (numels[t] + kChunk - 1) / kChunk;
+        if (nch > INT32_MAX || p->chunks.size() + (size_t)nch > (size_t)INT32_MAX) {
+            set_error("tensor list too large for one plan");
+            delete p;
+            return B200DDP_ETOOBIG;
+        }
+        for (int64_t c = 0; c < nch; ++c) p->chunks.push_back({t, (int)c});
+        off += (numels[t] + kBucketAlign - 1) / kBucketAlign * kBucketAlign;
+    }
+    p->bucket_elems = off;
+    p->h_ptrs.assign((size_t)kNumPtrKinds * (T > 0 ? T : 1), nullptr);
+    cudaError_t e = cudaSuccess;
+    const size_t nT = T > 0 ? T : 1, nC = p->chunks.empty() ? 1 : p->chunks.size();
+    if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_meta, sizeof(TensorMeta) * nT);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_chunks, sizeof(Chunk) * nC);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_ptrs, sizeof(void *) * kNumPtrKinds * nT);
+    if (e == cudaSuccess) e = cudaMemset(p->d_ptrs, 0, sizeof(void *) * kNumPtrKinds * nT);
+    if (e == cudaSuccess && T > 0)
+        e = cudaMemcpy(p->d_meta, p->meta.data(), sizeof(TensorMeta) * T, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && !p->chunks.empty())
+        e = cudaMemcpy(p->d_chunks, p->chunks.data(), sizeof(Chunk) * p->chunks.size(), cudaMemcpyHostToDevice);
+    for (int i = 0; i < b200ddp_plan::kRing && e == cudaSuccess; ++i) {
+        e = cudaMallocHost((void **)&p->pinned[i], sizeof(void *) * nT);
+        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->pinned_ev[i], cudaEventDisableTiming);
+    }
+    if (e != cudaSuccess) {
+        set_error("plan allocation failed: %s", cudaGetErrorString(e));
+        b200ddp_plan_destroy(p);
+        return B200DDP_ECUDA;
+    }
+    *out = p;
+    return B200DDP_OK;
+}
+
+int b200ddp_plan_destroy(b200ddp_plan *p) {
+    if (!p) return B200DDP_OK;
+    if (p->ctx) cudaSetDevice(p->ctx->device);
+    for (int i = 0; i < b200ddp_plan::kRing; ++i) {
+        if (p->pinned_ev[i]) {
+            cudaEventSynchronize(p->pinned_ev[i]);
+            cudaEventDestroy(p->pinned_ev[i]);
+        }
+        if (p->pinned[i]) cudaFreeHost(p->pinned[i]);
+    }
+    cudaFree(p->d_meta);
+    cudaFree(p->d_chunks);
+    cudaFree(p->d_ptrs);
+    delete p;
+    return B200DDP_OK;
+}
+
+int64_t b200ddp_plan_bucket_elems(const b200ddp_plan *plan) { return plan ? plan->bucket_elems : -1; }
+
+int b200ddp_plan_offsets(const b200ddp_plan *plan, int64_t *out) {
+    B2_REQUIRE(plan != nullptr && (out != nullptr || plan->T == 0), B200DDP_EINVAL, "NULL argument");
+    for (int t = 0; t < plan->T; ++t) out[t] = plan->meta[t].bucket_off;
+    return B200DDP_OK;
+}
+
+// ------------------------------------------------------------ K1 / unpack / K3
+int b200ddp_pack_scale(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads, void *bucket, float scale,
+                       b200ddp_stream stream) {
+    if (int rc = check_plan(ctx, plan)) return rc;
+    B2_REQUIRE(bucket != nullptr || plan->bucket_elems == 0, B200DDP_EINVAL, "bucket is NULL");
+    B2_REQUIRE(((uintptr_t)bucket & 15) == 0, B200DDP_EINVAL, "bucket must be 16-byte aligned");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = plan_upload(plan, kGradIn, grads, s)) return rc;
+    return launch_pack(plan_view(plan), plan->dtype, bucket, scale, ctx->sm_count, s);
+}
+
+int b200ddp_unpack(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, void *const *grads_out, float divisor,
+                   b200ddp_stream stream) {
+    if (int rc = check_plan(ctx, plan)) return rc;
+    B2_REQUIRE(bucket != nullptr || plan->bucket_elems == 0, B200DDP_EINVAL, "bucket is NULL");
+    B2_REQUIRE(((uintptr_t)bucket & 15) == 0, B200DDP_EINVAL, "bucket must be 16-byte aligned");
+    B2_REQUIRE(divisor != 0.0f && std::isfinite(divisor), B200DDP_EINVAL, "bad divisor");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = plan_upload(plan, kGradOut, (const void *const *)grads_out, s)) return rc;
+    return launch_unpack(plan_view(plan), plan->dtype, bucket, divisor, ctx->sm_count, s);
+}
+
+static int upload_update_tables(b200ddp_plan *plan, const SgdScalars &hp, void *const *params, void *const *moms,
+                                void *const *grads_out, cudaStream_t s) {
+    if (int rc = plan_upload(plan, kParam, (const void *const *)params, s)) return rc;
+    if (hp.has_momentum)
+        if (int rc = plan_upload(plan, kMom, (const void *const *)moms, s)) return rc;
+    if (grads_out)
+        if (int rc = plan_upload(plan, kGradOut, (const void *const *)grads_out, s)) return rc;
+    return B200DDP_OK;
+}
+
+int b200ddp_unpack_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, void *const *params,
+                       void *const *moms, void *const *grads_out, const b200ddp_sgd_args *args,
+                       b200ddp_stream stream) {
+    if (int rc = check_plan(ctx, plan)) return rc;
+    B2_REQUIRE(bucket != nullptr || plan->bucket_elems == 0, B200DDP_EINVAL, "bucket is NULL");
+    B2_REQUIRE(((uintptr_t)bucket & 15) == 0, B200DDP_EINVAL, "bucket must be 16-byte aligned");
+    SgdScalars hp;
+    if (int rc = sgd_scalars(args, &hp)) return rc;
+    if (plan->bucket_elems == 0) return B200DDP_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = upload_update_tables(plan, hp, params, moms, grads_out, s)) return rc;
+    return launch_update(plan_view(plan), plan->dtype, bucket, grads_out != nullptr, hp, ctx->sm_count, s);
+}
+
+int b200ddp_sgd_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads, void *const *params,
+                     void *const *moms, const b200ddp_sgd_args *args, b200ddp_stream stream) {
+    if (int rc = check_plan(ctx, plan)) return rc;
+    SgdScalars hp;
+    if (int rc = sgd_scalars(args, &hp)) return rc;
+    if (plan->bucket_elems == 0) return B200DDP_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = plan_upload(plan, kGradIn, grads, s)) return rc;
+    if (int rc = upload_update_tables(plan, hp, params, moms, nullptr, s)) return rc;
+    // direct mode: bucket == nullptr makes the kernel read ptrs[kGradIn]
+    return launch_update(plan_view(plan), B200DDP_F32, nullptr, false, hp, ctx->sm_count, s);
+}
+
+// ------------------------------------------------------------------------ K2
+int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype) {
+    if (!ctx) return B200DDP_EINVAL;
+    if (ctx->world == 1) return B200DDP_ALGO_ONESHOT;
+    const size_t bytes = (size_t)nelem * dtype_size(dtype);
+    if (!ctx->peers_ready) return ctx->nccl_comm ? (int)B200DDP_ALGO_NCCL : (int)B200DDP_ESTATE;
+    // one-shot moves (N-1) x S per GPU in one pass and wins while latency
+    // dominates; two-shot moves 2 (N-1)/N x S in two passes.
+    const size_t oneshot_max = (size_t)(ctx->world <= 2 ? 8 : ctx->world <= 4 ? 2 : 1) << 20;
+    return bytes <= oneshot_max ? B200DDP_ALGO_ONESHOT : B200DDP_ALGO_TWOSHOT;
+}
+
+int b200ddp_allreduce(b200ddp_ctx *ctx, size_t offset_bytes, int64_t nelem, int dtype, int algo,
+                      b200ddp_stream stream, size_t *result_offset_bytes) {
+    B2_REQUIRE(ctx != nullptr, B200DDP_EINVAL, "ctx is NULL");
+    if (int rc = in_staging(ctx, offset_bytes, nelem, dtype)) return rc;
+    if (result_offset_bytes) *result_offset_bytes = offset_bytes;
+    if (ctx->world == 1 || nelem == 0) return B200DDP_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (algo == B200DDP_ALGO_AUTO) {
+        algo = b200ddp_allreduce_pick(ctx, nelem, dtype);
+        B2_REQUIRE(algo > 0, B200DDP_ESTATE, "no collective is set up: call b200ddp_ipc_open_peers or b200ddp_nccl_init");
+    }
+    if (algo == B200DDP_ALGO_NCCL) {
+        B2_REQUIRE(ctx->nccl_comm != nullptr, B200DDP_ESTATE, "NCCL communicator not initialised");
+        return nccl_allreduce(ctx, ctx->staging + offset_bytes, nelem, dtype, s);
+    }
+    B2_REQUIRE(algo == B200DDP_ALGO_ONESHOT || algo == B200DDP_ALGO_TWOSHOT, B200DDP_EINVAL, "bad algo %d", algo);
+    B2_REQUIRE(ctx->peers_ready, B200DDP_ESTATE, "peer memory not opened");
+    if (algo == B200DDP_ALGO_ONESHOT && result_offset_bytes) *result_offset_bytes = ctx->staging_bytes + offset_bytes;
+    return launch_p2p_allreduce(ctx, offset_bytes, nelem, dtype, algo, s);
+}
+
+int b200ddp_allreduce_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, size_t offset_bytes, void *const *params,
+                          void *const *moms, void *const *grads_out, const b200ddp_sgd_args *args,
+                          b200ddp_stream stream) {
+    if (int rc = check_plan(ctx, plan)) return rc;
+    if (int rc = in_staging(ctx, offset_bytes, plan->bucket_elems, plan->dtype)) return rc;
+    SgdScalars hp;
+    if (int rc = sgd_scalars(args, &hp)) return rc;
+    if (plan->bucket_elems == 0) return B200DDP_OK;
+    B2_REQUIRE(ctx->peers_ready, B200DDP_ESTATE, "peer memory not opened");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    cudaStream_t s = (cudaStream_t)stream;
+    if (int rc = upload_update_tables(plan, hp, params, moms, grads_out, s)) return rc;
+    if (ctx->world == 1)
+        return launch_update(plan_view(plan), plan->dtype, ctx->staging + offset_bytes, grads_out != nullptr, hp,
+                             ctx->sm_count, s);
+    return launch_oneshot_update(ctx, plan_view(plan), plan->dtype, offset_bytes, grads_out != nullptr, hp, s);
+}
+
+// ----------------------------------------------------------------- emulation
+static int check_emu(b200ddp_ctx *const *ctxs, int n) {
+    B2_REQUIRE(ctxs != nullptr && n >= 2 && n <= B200DDP_MAX_WORLD, B200DDP_EINVAL, "bad emulated world %d", n);
+    for (int r = 0; r < n; ++r) {
+        B2_REQUIRE(ctxs[r] != nullptr, B200DDP_EINVAL, "ctx %d is NULL", r);
+        B2_REQUIRE(ctxs[r]->world == n && ctxs[r]->rank == r, B200DDP_EINVAL, "ctx %d has rank %d / world %d", r,
+                   ctxs[r]->rank, ctxs[r]->world);
+        B2_REQUIRE(ctxs[r]->device == ctxs[0]->device, B200DDP_EINVAL, "emulated ranks must share one device");
+        B2_REQUIRE(ctxs[r]->peers_ready, B200DDP_ESTATE, "ctx %d has no peers", r);
+        B2_REQUIRE(ctxs[r]->staging_bytes == ctxs[0]->staging_bytes && ctxs[r]->epoch == ctxs[0]->epoch,
+                   B200DDP_ESTATE, "emulated contexts out of step");
+    }
+    return B200DDP_OK;
+}
+
+int b200ddp_emu_allreduce(b200ddp_ctx *const *ctxs, int n, size_t offset_bytes, int64_t nelem, int dtype, int algo,
+                          b200ddp_stream stream, size_t *result_offset_bytes) {
+    if (int rc = check_emu(ctxs, n)) return rc;
+    if (int rc = in_staging(ctxs[0], offset_bytes, nelem, dtype)) return rc;
+    if (algo == B200DDP_ALGO_AUTO) algo = b200ddp_allreduce_pick(ctxs[0], nelem, dtype);
+    B2_REQUIRE(algo == B200DDP_ALGO_ONESHOT || algo == B200DDP_ALGO_TWOSHOT, B200DDP_EINVAL,
+               "emulation covers the P2P algorithms only (got %d)", algo);
+    if (result_offset_bytes)
+        *result_offset_bytes = algo == B200DDP_ALGO_ONESHOT ? ctxs[0]->staging_bytes + offset_bytes : offset_bytes;
+    if (nelem == 0) return B200DDP_OK;
+    B2_CHECK_CUDA(cudaSetDevice(ctxs[0]->device));
+    return launch_p2p_allreduce_emu(ctxs, n, offset_bytes, nelem, dtype, algo, (cudaStream_t)stream);
+}
+
+int b200ddp_emu_allreduce_sgd(b200ddp_ctx *const *ctxs, b200ddp_plan *const *plans, int n, size_t offset_bytes,
+                              void *const *const *params, void *const *const *moms,
+                              void *const *const *grads_out, const b200ddp_sgd_args *args, b200ddp_stream stream) {
+    if (int rc = check_emu(ctxs, n)) return rc;
+    B2_REQUIRE(plans != nullptr && params != nullptr, B200DDP_EINVAL, "NULL argument");
+    SgdScalars hp;
+    if (int rc = sgd_scalars(args, &hp)) return rc;
+    B2_REQUIRE(!hp.has_momentum || moms != nullptr, B200DDP_EINVAL, "momentum buffers missing");
+    cudaStream_t s = (cudaStream_t)stream;
+    B2_CHECK_CUDA(cudaSetDevice(ctxs[0]->device));
+    PlanView pvs[B200DDP_MAX_WORLD];
+    for (int r = 0; r < n; ++r) {
+        if (int rc = check_plan(ctxs[r], plans[r])) return rc;
+        B2_REQUIRE(plans[r]->bucket_elems == plans[0]->bucket_elems && plans[r]->T == plans[0]->T &&
+                       plans[r]->dtype == plans[0]->dtype,
+                   B200DDP_EINVAL, "plans differ across emulated ranks");
+        if (int rc = upload_update_tables(plans[r], hp, params[r], moms ? moms[r] : nullptr,
+                                          grads_out ? grads_out[r] : nullptr, s))
+            return rc;
+        pvs[r] = plan_view(plans[r]);
+    }
+    if (int rc = in_staging(ctxs[0], offset_bytes, plans[0]->bucket_elems, plans[0]->dtype)) return rc;
+    if (plans[0]->bucket_elems == 0) return B200DDP_OK;
+    return launch_oneshot_update_emu(ctxs, pvs, n, plans[0]->dtype, offset_bytes, grads_out != nullptr, hp, s);
+}
+
+// ------------------------------------------------------------------------ K4
+int b200ddp_sampler_sizes(int64_t n, int world, int drop_last, int64_t *num_samples, int64_t *total_size) {
+    B2_REQUIRE(n >= 0 && world >= 1, B200DDP_EINVAL, "bad sampler geometry n=%lld world=%d", (long long)n, world);
+    int64_t num;
+    if (drop_last && n % world != 0) {
+        const int64_t a = n - world;   // ceil((n - world) / world), torch/utils/data/distributed.py:98-100
+        num = a >= 0 ? (a + world - 1) / world : -((-a) / world);
+    } else {
+        num = (n + world - 1) / world;   // :102
+    }
+    if (num_samples) *num_samples = num;
+    if (total_size) *total_size = num * world;
+    return B200DDP_OK;
+}
+
+int b200ddp_sampler_shard(b200ddp_ctx *ctx, int64_t n, int world, int rank, uint64_t seed, uint64_t epoch,
+                          int shuffle, int drop_last, int64_t *out_dev, b200ddp_stream stream) {
+    B2_REQUIRE(ctx != nullptr, B200DDP_EINVAL, "ctx is NULL");
+    B2_REQUIRE(world >= 1, B200DDP_EINVAL, "num_replicas must be positive");
+    B2_REQUIRE(rank >= 0 && rank < world, B200DDP_EINVAL, "Invalid rank %d, rank should be in the interval [0, %d]",
+               rank, world - 1);
+    B2_REQUIRE(n >= 0 && n < (int64_t)(0xffffffffu / 20), B200DDP_ETOOBIG,
+               "dataset length %lld is outside the 32-bit randperm range", (long long)n);
+    int64_t num = 0;
+    if (int rc = b200ddp_sampler_sizes(n, world, drop_last, &num, nullptr)) return rc;
+    if (num <= 0 || n == 0) return B200DDP_OK;
+    B2_REQUIRE(out_dev != nullptr, B200DDP_EINVAL, "out_dev is NULL");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    return launch_sampler(ctx, n, world, rank, seed + epoch, shuffle, num, out_dev, (cudaStream_t)stream);
+}
+
+}  // extern "C"

@@ -1,0 +1,363 @@
+// K2: all-reduce of a staging bucket by direct peer loads/stores over NVLink,
+// and the fused one-shot-reduce + momentum-SGD kernel.
+//
+// Every rank launches the same grid.  Block b of rank r synchronises with block
+// b of every peer through flags in peer memory: flag[b][src] on rank dst is
+// written only by block b of rank src, with a generation number that increases
+// by two per launch (never reset, so no host sync between launches).
+//
+//   one-shot : barrier | every rank reads the whole bucket of all N ranks, sums
+//              in rank order (so all ranks get identical bits), writes the result
+//              out of place | barrier (peers are done reading my bucket)
+//   two-shot : barrier | rank r reduces slice r of all N buckets and stores the
+//              sums into slice r of all N buckets | barrier (all slices landed)
+//
+// EMU = true runs all N ranks as blockIdx.y of ONE cooperative launch on one
+// GPU: kernels that spin on each other's flags must not be separate launches
+// on the same device.
+#include <cuda_bf16.h>
+
+#include "device_utils.cuh"
+
+namespace b200ddp {
+
+namespace {
+
+constexpr int kP2PThreads = 512;
+
+__device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t *p) {
+    uint32_t v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+// Peer data: plain weak loads, ordered behind the barrier's acquire; no L1 allocation.
+__device__ __forceinline__ uint4 ld_peer_u4(const void *p) {
+    uint4 r;
+    asm volatile("ld.global.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p)
+                 : "memory");
+    return r;
+}
+__device__ __forceinline__ void st_peer_u4(void *p, const uint4 &v) {
+    asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// All threads of the block call this.  Orders every earlier write of the block
+// (release, cumulative over the bar.sync) before the flag, and every later read
+// after the peers' flags (acquire, then bar.sync).
+__device__ __forceinline__ void peer_barrier(const PeerTable &pt, int rank, int world, int bid, uint32_t gen) {
+    __syncthreads();
+    if ((int)threadIdx.x < world) {
+        const int peer = threadIdx.x;
+        st_release_sys(pt.flags[peer] + bid * B200DDP_MAX_WORLD + rank, gen);
+        const uint32_t *mine = pt.flags[rank] + bid * B200DDP_MAX_WORLD + peer;
+        while ((int32_t)(ld_acquire_sys(mine) - gen) < 0) {
+        }
+    }
+    __syncthreads();
+}
+
+// ---- 16-byte vector arithmetic in fp32 ---------------------------------------
+template <typename BT> struct Vec16;
+template <> struct Vec16<float> {
+    static constexpr int kAcc = 4;
+    static __device__ __forceinline__ void zero(float *a) { a[0] = a[1] = a[2] = a[3] = 0.f; }
+    static __device__ __forceinline__ void set(float *a, const uint4 &v) {
+        a[0] = __uint_as_float(v.x); a[1] = __uint_as_float(v.y); a[2] = __uint_as_float(v.z); a[3] = __uint_as_float(v.w);
+    }
+    static __device__ __forceinline__ void add(float *a, const uint4 &v) {
+        a[0] = __fadd_rn(a[0], __uint_as_float(v.x)); a[1] = __fadd_rn(a[1], __uint_as_float(v.y));
+        a[2] = __fadd_rn(a[2], __uint_as_float(v.z)); a[3] = __fadd_rn(a[3], __uint_as_float(v.w));
+    }
+    static __device__ __forceinline__ uint4 pack(const float *a) {
+        return make_uint4(__float_as_uint(a[0]), __float_as_uint(a[1]), __float_as_uint(a[2]), __float_as_uint(a[3]));
+    }
+};
+template <> struct Vec16<__nv_bfloat16> {
+    static constexpr int kAcc = 8;
+    static __device__ __forceinline__ void set(float *a, const uint4 &v) {
+        const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { a[2 * i] = __uint_as_float(w[i] << 16); a[2 * i + 1] = __uint_as_float(w[i] & 0xffff0000u); }
+    }
+    static __device__ __forceinline__ void add(float *a, const uint4 &v) {
+        const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            a[2 * i] = __fadd_rn(a[2 * i], __uint_as_float(w[i] << 16));
+            a[2 * i + 1] = __fadd_rn(a[2 * i + 1], __uint_as_float(w[i] & 0xffff0000u));
+        }
+    }
+    static __device__ __forceinline__ uint4 pack(const float *a) {   // one rounding, after the fp32 sum
+        unsigned w[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            __nv_bfloat162 h = __floats2bfloat162_rn(a[2 * i], a[2 * i + 1]);
+            w[i] = *reinterpret_cast<unsigned *>(&h);
+        }
+        return make_uint4(w[0], w[1], w[2], w[3]);
+    }
+};
+
+struct P2PArgs {
+    PeerTable pt;
+    int rank, world;
+    size_t off_bytes;       // bucket inside the first staging half
+    size_t result_off;      // one-shot: where the sums go (own staging)
+    int64_t nvec;           // 16-byte vectors in the bucket
+    uint32_t gen;           // barrier generations gen+1, gen+2
+};
+
+// N > 0: unrolled for that world size; N == 0: runtime loop over args.world.
+template <typename BT, int N, bool EMU>
+__global__ void __launch_bounds__(kP2PThreads) oneshot_kernel(P2PArgs a) {
+    const int rank = EMU ? (int)blockIdx.y : a.rank;
+    const int world = N > 0 ? N : a.world;
+    const int bid = blockIdx.x;
+    peer_barrier(a.pt, rank, world, bid, a.gen + 1);
+    uint4 *dst = reinterpret_cast<uint4 *>(a.pt.staging[rank] + a.result_off);
+    const int64_t stride = (int64_t)gridDim.x * kP2PThreads;
+    for (int64_t i = (int64_t)bid * kP2PThreads + threadIdx.x; i < a.nvec; i += stride) {
+        float acc[Vec16<BT>::kAcc];
+        if (N > 0) {
+            uint4 v[N > 0 ? N : 1];
+#pragma unroll
+            for (int r = 0; r < N; ++r) v[r] = ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i);
+            Vec16<BT>::set(acc, v[0]);
+#pragma unroll
+            for (int r = 1; r < N; ++r) Vec16<BT>::add(acc, v[r]);
+        } else {
+            Vec16<BT>::set(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[0] + a.off_bytes) + i));
+            for (int r = 1; r < world; ++r)
+                Vec16<BT>::add(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i));
+        }
+        dst[i] = Vec16<BT>::pack(acc);
+    }
+    peer_barrier(a.pt, rank, world, bid, a.gen + 2);
+}
+
+template <typename BT, int N, bool EMU>
+__global__ void __launch_bounds__(kP2PThreads) twoshot_kernel(P2PArgs a) {
+    const int rank = EMU ? (int)blockIdx.y : a.rank;
+    const int world = N > 0 ? N : a.world;
+    const int bid = blockIdx.x;
+    peer_barrier(a.pt, rank, world, bid, a.gen + 1);
+    const int64_t per = (a.nvec + world - 1) / world;
+    const int64_t lo = per * rank;
+    const int64_t hi = lo + per < a.nvec ? lo + per : a.nvec;
+    const int64_t stride = (int64_t)gridDim.x * kP2PThreads;
+    for (int64_t i = lo + (int64_t)bid * kP2PThreads + threadIdx.x; i < hi; i += stride) {
+        float acc[Vec16<BT>::kAcc];
+        if (N > 0) {
+            uint4 v[N > 0 ? N : 1];
+#pragma unroll
+            for (int r = 0; r < N; ++r) v[r] = ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i);
+            Vec16<BT>::set(acc, v[0]);
+#pragma unroll
+            for (int r = 1; r < N; ++r) Vec16<BT>::add(acc, v[r]);
+        } else {
+            Vec16<BT>::set(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[0] + a.off_bytes) + i));
+            for (int r = 1; r < world; ++r)
+                Vec16<BT>::add(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i));
+        }
+        const uint4 out = Vec16<BT>::pack(acc);
+        if (N > 0) {
+#pragma unroll
+            for (int r = 0; r < N; ++r) st_peer_u4(reinterpret_cast<uint4 *>(a.pt.staging[r] + a.off_bytes) + i, out);
+        } else {
+            for (int r = 0; r < world; ++r) st_peer_u4(reinterpret_cast<uint4 *>(a.pt.staging[r] + a.off_bytes) + i, out);
+        }
+    }
+    peer_barrier(a.pt, rank, world, bid, a.gen + 2);
+}
+
+// ---- fused one-shot reduce + update --------------------------------------------
+template <bool EMU> struct PlanSet { PlanView v[EMU ? B200DDP_MAX_WORLD : 1]; };
+
+template <typename BT, bool WRITE_GRAD, bool EMU>
+__global__ void __launch_bounds__(kThreads) oneshot_update_kernel(P2PArgs a, PlanSet<EMU> ps, SgdScalars hp) {
+    const int rank = EMU ? (int)blockIdx.y : a.rank;
+    const int world = a.world;
+    const int bid = blockIdx.x;
+    const PlanView &pv = ps.v[EMU ? rank : 0];
+    const int tid = threadIdx.x;
+    const bool load_m = hp.has_momentum && !hp.first_step;
+    peer_barrier(a.pt, rank, world, bid, a.gen + 1);
+    for (int c = bid; c < pv.nchunks; c += gridDim.x) {
+        const Chunk ck = pv.chunks[c];
+        const TensorMeta tm = pv.meta[ck.tensor];
+        const int64_t e0 = (int64_t)ck.index * kChunk;
+        const int64_t left = tm.numel - e0;
+        const int count = left < kChunk ? (int)left : kChunk;
+        const int64_t boff = tm.bucket_off + e0;
+        float *p = (float *)pv.ptrs[kParam][ck.tensor] + e0;
+        float *m = hp.has_momentum ? (float *)pv.ptrs[kMom][ck.tensor] + e0 : nullptr;
+        float *go = WRITE_GRAD ? (float *)pv.ptrs[kGradOut][ck.tensor] + e0 : nullptr;
+        const bool aligned = (((uintptr_t)p | (uintptr_t)m | (uintptr_t)go) & 15) == 0;   // bucket side is aligned by layout
+        const int nvec = aligned ? count / kVec : 0;
+        for (int i = tid; i < nvec; i += kThreads) {
+            const int o = i * kVec;
+            // all peers' loads are issued before the first add (NVLink round trips overlap)
+            float4 gr[B200DDP_MAX_WORLD];
+#pragma unroll
+            for (int r = 0; r < B200DDP_MAX_WORLD; ++r)
+                if (r < world) gr[r] = Bucket<BT>::load4c(reinterpret_cast<const BT *>(a.pt.staging[r] + a.off_bytes) + boff + o);
+            float4 gs = gr[0];
+#pragma unroll
+            for (int r = 1; r < B200DDP_MAX_WORLD; ++r)
+                if (r < world) {
+                    gs.x = __fadd_rn(gs.x, gr[r].x); gs.y = __fadd_rn(gs.y, gr[r].y);
+                    gs.z = __fadd_rn(gs.z, gr[r].z); gs.w = __fadd_rn(gs.w, gr[r].w);
+                }
+            float4 p4 = ld_rmw_f4(p + o), m4, ga;
+            if (load_m) m4 = ld_rmw_f4(m + o);
+            sgd_elem4(gs, p4, m4, ga, hp);
+            st_f4(p + o, p4);
+            if (hp.has_momentum) st_f4(m + o, m4);
+            if (WRITE_GRAD) st_f4(go + o, ga);
+        }
+        for (int i = nvec * kVec + tid; i < count; i += kThreads) {
+            float g1[B200DDP_MAX_WORLD];
+#pragma unroll
+            for (int r = 0; r < B200DDP_MAX_WORLD; ++r)
+                if (r < world) g1[r] = Bucket<BT>::load1c(reinterpret_cast<const BT *>(a.pt.staging[r] + a.off_bytes) + boff + i);
+            float gs = g1[0];
+#pragma unroll
+            for (int r = 1; r < B200DDP_MAX_WORLD; ++r)
+                if (r < world) gs = __fadd_rn(gs, g1[r]);
+            float ps1 = p[i], ms = load_m ? m[i] : 0.f, ga;
+            sgd_elem(gs, ps1, ms, ga, hp);
+            p[i] = ps1;
+            if (hp.has_momentum) m[i] = ms;
+            if (WRITE_GRAD) go[i] = ga;
+        }
+    }
+    peer_barrier(a.pt, rank, world, bid, a.gen + 2);
+}
+
+#define B2_LAUNCH_CHECK()                                                                              \
+    do {                                                                                               \
+        cudaError_t _e = cudaGetLastError();                                                           \
+        if (_e != cudaSuccess) {                                                                       \
+            set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
+            return B200DDP_ECUDA;                                                                      \
+        }                                                                                              \
+    } while (0)
+
+template <typename BT, int N, bool EMU> const void *pick_kernel(int algo) {
+    return algo == B200DDP_ALGO_ONESHOT ? (const void *)oneshot_kernel<BT, N, EMU> : (const void *)twoshot_kernel<BT, N, EMU>;
+}
+template <typename BT, bool EMU> const void *pick_world(int algo, int world) {
+    switch (world) {
+        case 2: return pick_kernel<BT, 2, EMU>(algo);
+        case 4: return pick_kernel<BT, 4, EMU>(algo);
+        case 8: return pick_kernel<BT, 8, EMU>(algo);
+        default: return pick_kernel<BT, 0, EMU>(algo);
+    }
+}
+template <bool EMU> const void *pick(int dtype, int algo, int world) {
+    return dtype == B200DDP_F32 ? pick_world<float, EMU>(algo, world) : pick_world<__nv_bfloat16, EMU>(algo, world);
+}
+
+P2PArgs make_args(const b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype) {
+    P2PArgs a;
+    a.pt = ctx->peers;
+    a.rank = ctx->rank;
+    a.world = ctx->world;
+    a.off_bytes = off;
+    a.result_off = ctx->staging_bytes + off;
+    a.nvec = nelem * (dtype == B200DDP_BF16 ? 2 : 4) / 16;
+    a.gen = ctx->epoch;
+    return a;
+}
+
+}  // namespace
+
+// Same on every rank: a pure function of the bucket and the world size.
+int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int sm_count) {
+    int64_t nvec = nelem * (dtype == B200DDP_BF16 ? 2 : 4) / 16;
+    if (algo == B200DDP_ALGO_TWOSHOT) nvec = (nvec + world - 1) / world;
+    // two vectors per thread per pass keeps enough loads in flight for the NVLink round trip
+    int64_t g = (nvec + 2 * kP2PThreads - 1) / (2 * kP2PThreads);
+    const int cap = 2 * sm_count < kMaxBlocksP2P ? 2 * sm_count : kMaxBlocksP2P;
+    if (g < 1) g = 1;
+    if (g > cap) g = cap;
+    return (int)g;
+}
+
+int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, int algo, cudaStream_t s) {
+    P2PArgs a = make_args(ctx, off, nelem, dtype);
+    const int grid = p2p_grid_for(nelem, dtype, algo, ctx->world, kSmCount);
+    const void *k = pick<false>(dtype, algo, ctx->world);
+    void *params[] = {&a};
+    B2_CHECK_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kP2PThreads), params, 0, s));
+    ctx->epoch += 2;
+    return B200DDP_OK;
+}
+
+int launch_p2p_allreduce_emu(b200ddp_ctx *const *ctxs, int n, size_t off, int64_t nelem, int dtype, int algo,
+                             cudaStream_t s) {
+    P2PArgs a = make_args(ctxs[0], off, nelem, dtype);
+    const void *k = pick<true>(dtype, algo, n);
+    int per_sm = 0;
+    B2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kP2PThreads, 0));
+    int grid = p2p_grid_for(nelem, dtype, algo, n, kSmCount);
+    const int fit = per_sm * ctxs[0]->sm_count / n;   // all ranks' blocks must be co-resident
+    B2_REQUIRE(fit >= 1, B200DDP_ESTATE, "device cannot co-schedule %d emulated ranks", n);
+    if (grid > fit) grid = fit;
+    void *params[] = {&a};
+    B2_CHECK_CUDA(cudaLaunchCooperativeKernel(k, dim3(grid, n), dim3(kP2PThreads), params, 0, s));
+    for (int r = 0; r < n; ++r) ctxs[r]->epoch += 2;
+    return B200DDP_OK;
+}
+
+static int update_grid(int nchunks) { return nchunks < 2 * kSmCount ? nchunks : 2 * kSmCount; }
+
+int launch_oneshot_update(b200ddp_ctx *ctx, const PlanView &pv, int dtype, size_t off, bool write_grad,
+                          const SgdScalars &hp, cudaStream_t s) {
+    P2PArgs a = make_args(ctx, off, 0, dtype);
+    PlanSet<false> ps;
+    ps.v[0] = pv;
+    const int grid = update_grid(pv.nchunks);
+#define B2_FUSED(BT, WG) oneshot_update_kernel<BT, WG, false><<<grid, kThreads, 0, s>>>(a, ps, hp)
+    if (dtype == B200DDP_F32) {
+        if (write_grad) B2_FUSED(float, true); else B2_FUSED(float, false);
+    } else {
+        if (write_grad) B2_FUSED(__nv_bfloat16, true); else B2_FUSED(__nv_bfloat16, false);
+    }
+#undef B2_FUSED
+    B2_LAUNCH_CHECK();
+    ctx->epoch += 2;
+    return B200DDP_OK;
+}
+
+int launch_oneshot_update_emu(b200ddp_ctx *const *ctxs, const PlanView *pvs, int n, int dtype, size_t off,
+                              bool write_grad, const SgdScalars &hp, cudaStream_t s) {
+    P2PArgs a = make_args(ctxs[0], off, 0, dtype);
+    PlanSet<true> ps;
+    for (int r = 0; r < n; ++r) ps.v[r] = pvs[r];
+    for (int r = n; r < B200DDP_MAX_WORLD; ++r) ps.v[r] = pvs[0];
+    const void *k;
+    if (dtype == B200DDP_F32)
+        k = write_grad ? (const void *)oneshot_update_kernel<float, true, true> : (const void *)oneshot_update_kernel<float, false, true>;
+    else
+        k = write_grad ? (const void *)oneshot_update_kernel<__nv_bfloat16, true, true>
+                       : (const void *)oneshot_update_kernel<__nv_bfloat16, false, true>;
+    int per_sm = 0;
+    B2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kThreads, 0));
+    int grid = update_grid(pvs[0].nchunks);
+    const int fit = per_sm * ctxs[0]->sm_count / n;
+    B2_REQUIRE(fit >= 1, B200DDP_ESTATE, "device cannot co-schedule %d emulated ranks", n);
+    if (grid > fit) grid = fit;
+    SgdScalars h = hp;
+    void *params[] = {&a, &ps, &h};
+    B2_CHECK_CUDA(cudaLaunchCooperativeKernel(k, dim3(grid, n), dim3(kThreads), params, 0, s));
+    for (int r = 0; r < n; ++r) ctxs[r]->epoch += 2;
+    return B200DDP_OK;
+}
+
+}  // namespace b200ddp

@@ -1,0 +1,240 @@
+"""Context and plan objects over the C ABI, and the per-process default context.
+
+One process per GPU: the context is created on the current CUDA device with
+the rank / world size of the default torch.distributed group (1 rank when no
+group is initialised, as the reference's get_world_size() does -
+codes/task2/dist_utils.py:26-30).  Peer-memory handles and the NCCL id travel
+through torch.distributed; nothing else does.
+"""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import byref, c_int64, c_size_t, c_void_p
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+from ._lib import B200DDPError, SgdArgs, check, ptr_array
+
+_DTYPES = {"fp32": _lib.F32, "float32": _lib.F32, torch.float32: _lib.F32,
+           "bf16": _lib.BF16, "bfloat16": _lib.BF16, torch.bfloat16: _lib.BF16,
+           _lib.F32: _lib.F32, _lib.BF16: _lib.BF16}
+_TORCH_DTYPE = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16}
+_ESIZE = {_lib.F32: 4, _lib.BF16: 2}
+
+
+def dtype_code(d) -> int:
+    try:
+        return _DTYPES[d]
+    except KeyError:
+        raise ValueError(f"bucket dtype must be fp32 or bf16, got {d!r}") from None
+
+
+def _require_cuda():
+    if not torch.cuda.is_available():
+        raise B200DDPError("b200ddp needs a CUDA device (sm_100a); there is no CPU fallback")
+
+
+def _stream_handle(stream=None) -> c_void_p:
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return c_void_p(s.cuda_stream)
+
+
+class Plan:
+    """Bucket layout of a list of fp32 tensors (immutable)."""
+
+    def __init__(self, ctx: "Context", numels, bucket_dtype="fp32"):
+        self.ctx = ctx
+        self.numels = [int(n) for n in numels]
+        self.T = len(self.numels)
+        self.dtype = dtype_code(bucket_dtype)
+        self.esize = _ESIZE[self.dtype]
+        arr = (c_int64 * max(self.T, 1))(*self.numels)
+        h = c_void_p()
+        check(_lib.lib().b200ddp_plan_create(ctx.handle, self.T, arr, self.dtype, byref(h)), "plan_create")
+        self.handle = h
+        self.bucket_elems = int(_lib.lib().b200ddp_plan_bucket_elems(h))
+        offs = (c_int64 * max(self.T, 1))()
+        check(_lib.lib().b200ddp_plan_offsets(h, offs), "plan_offsets")
+        self.offsets = list(offs)[: self.T]
+        self.bucket_bytes = self.bucket_elems * self.esize
+
+    def close(self):
+        if getattr(self, "handle", None):
+            _lib.lib().b200ddp_plan_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class Context:
+    """Per-GPU state: peer-visible staging, barrier flags, NCCL communicator."""
+
+    def __init__(self, rank=0, world=1, device=None, staging_bytes=None):
+        _require_cuda()
+        if device is None:
+            device = torch.cuda.current_device()
+        if staging_bytes is None:
+            staging_bytes = int(os.environ.get("B200DDP_STAGING_MB", "256")) << 20
+        self.rank, self.world, self.device = int(rank), int(world), int(device)
+        h = c_void_p()
+        check(_lib.lib().b200ddp_create(self.rank, self.world, self.device, int(staging_bytes), byref(h)), "create")
+        self.handle = h
+        p, n = c_void_p(), c_size_t()
+        check(_lib.lib().b200ddp_staging(h, byref(p), byref(n)), "staging")
+        self.staging_ptr, self.staging_bytes = int(p.value), int(n.value)
+        f = c_void_p()
+        check(_lib.lib().b200ddp_flags(h, byref(f)), "flags")
+        self.flags_ptr = int(f.value)
+        self.has_nccl = False
+        self.has_peers = self.world == 1
+
+    # ---- set-up --------------------------------------------------------------
+    def connect(self, group=None, nccl=True, p2p=True):
+        """Collective over `group`: open every peer's staging (CUDA IPC) and join
+        the library's own NCCL communicator."""
+        if self.world == 1:
+            return self
+        if p2p and not self.has_peers:
+            mine = ctypes.create_string_buffer(_lib.IPC_BYTES)
+            check(_lib.lib().b200ddp_ipc_export(self.handle, mine), "ipc_export")
+            handles = [None] * self.world
+            dist.all_gather_object(handles, bytes(mine.raw), group=group)
+            blob = ctypes.create_string_buffer(b"".join(handles), _lib.IPC_BYTES * self.world)
+            check(_lib.lib().b200ddp_ipc_open_peers(self.handle, blob), "ipc_open_peers")
+            self.has_peers = True
+        if nccl and not self.has_nccl:
+            uid = ctypes.create_string_buffer(_lib.NCCL_UID_BYTES)
+            if self.rank == 0:
+                check(_lib.lib().b200ddp_nccl_unique_id(uid), "nccl_unique_id")
+            box = [bytes(uid.raw)]
+            dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+            uid = ctypes.create_string_buffer(box[0], _lib.NCCL_UID_BYTES)
+            check(_lib.lib().b200ddp_nccl_init(self.handle, uid), "nccl_init")
+            self.has_nccl = True
+        return self
+
+    def link_local(self, peers: "list[Context]"):
+        """Same-process peers (one process driving several contexts)."""
+        st = ptr_array([c.staging_ptr for c in peers])
+        fl = ptr_array([c.flags_ptr for c in peers])
+        check(_lib.lib().b200ddp_set_peers_direct(self.handle, st, fl), "set_peers_direct")
+        self.has_peers = True
+        return self
+
+    def close(self):
+        if getattr(self, "handle", None):
+            _lib.lib().b200ddp_destroy(self.handle)
+            self.handle = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- views ---------------------------------------------------------------
+    def plan(self, numels, bucket_dtype="fp32") -> Plan:
+        return Plan(self, numels, bucket_dtype)
+
+    def bucket_ptr(self, offset_bytes: int) -> int:
+        return self.staging_ptr + int(offset_bytes)
+
+    # ---- kernels ---------------------------------------------------------------
+    def pack_scale(self, plan: Plan, grad_ptrs, bucket_ptr: int, scale: float, stream=None):
+        check(_lib.lib().b200ddp_pack_scale(self.handle, plan.handle, ptr_array(grad_ptrs), c_void_p(bucket_ptr),
+                                            float(scale), _stream_handle(stream)), "pack_scale")
+
+    def unpack(self, plan: Plan, bucket_ptr: int, grad_out_ptrs, divisor: float = 1.0, stream=None):
+        check(_lib.lib().b200ddp_unpack(self.handle, plan.handle, c_void_p(bucket_ptr), ptr_array(grad_out_ptrs),
+                                        float(divisor), _stream_handle(stream)), "unpack")
+
+    def allreduce(self, offset_bytes: int, nelem: int, dtype, algo="auto", stream=None) -> int:
+        """Returns the staging offset (bytes) at which the sums are."""
+        res = c_size_t()
+        a = _lib.ALGO_NAMES[algo] if isinstance(algo, str) else int(algo)
+        check(_lib.lib().b200ddp_allreduce(self.handle, int(offset_bytes), int(nelem), dtype_code(dtype), a,
+                                           _stream_handle(stream), byref(res)), "allreduce")
+        return int(res.value)
+
+    def allreduce_pick(self, nelem: int, dtype) -> int:
+        return int(_lib.lib().b200ddp_allreduce_pick(self.handle, int(nelem), dtype_code(dtype)))
+
+    def unpack_sgd(self, plan: Plan, bucket_ptr: int, param_ptrs, mom_ptrs, grad_out_ptrs, args: SgdArgs, stream=None):
+        check(_lib.lib().b200ddp_unpack_sgd(
+            self.handle, plan.handle, c_void_p(bucket_ptr), ptr_array(param_ptrs),
+            ptr_array(mom_ptrs) if mom_ptrs is not None else None,
+            ptr_array(grad_out_ptrs) if grad_out_ptrs is not None else None,
+            byref(args), _stream_handle(stream)), "unpack_sgd")
+
+    def sgd_step(self, plan: Plan, grad_ptrs, param_ptrs, mom_ptrs, args: SgdArgs, stream=None):
+        check(_lib.lib().b200ddp_sgd_step(
+            self.handle, plan.handle, ptr_array(grad_ptrs), ptr_array(param_ptrs),
+            ptr_array(mom_ptrs) if mom_ptrs is not None else None, byref(args), _stream_handle(stream)), "sgd_step")
+
+    def allreduce_sgd(self, plan: Plan, offset_bytes: int, param_ptrs, mom_ptrs, grad_out_ptrs, args: SgdArgs,
+                      stream=None):
+        check(_lib.lib().b200ddp_allreduce_sgd(
+            self.handle, plan.handle, int(offset_bytes), ptr_array(param_ptrs),
+            ptr_array(mom_ptrs) if mom_ptrs is not None else None,
+            ptr_array(grad_out_ptrs) if grad_out_ptrs is not None else None,
+            byref(args), _stream_handle(stream)), "allreduce_sgd")
+
+    def sampler_shard(self, n, world, rank, seed, epoch, shuffle, drop_last, stream=None) -> torch.Tensor:
+        """int64 CUDA tensor holding this rank's indices."""
+        num = sampler_sizes(n, world, drop_last)[0]
+        # rank / geometry errors must surface even when the shard is empty
+        out = torch.empty(max(num, 0), dtype=torch.int64, device=torch.device("cuda", self.device))
+        check(_lib.lib().b200ddp_sampler_shard(self.handle, int(n), int(world), int(rank),
+                                               int(seed) & 0xFFFFFFFFFFFFFFFF, int(epoch) & 0xFFFFFFFFFFFFFFFF,
+                                               int(bool(shuffle)), int(bool(drop_last)),
+                                               c_void_p(out.data_ptr()) if num > 0 else None,
+                                               _stream_handle(stream)), "sampler_shard")
+        return out
+
+
+def sampler_sizes(n: int, world: int, drop_last: bool) -> tuple[int, int]:
+    num, total = c_int64(), c_int64()
+    check(_lib.lib().b200ddp_sampler_sizes(int(n), int(world), int(bool(drop_last)), byref(num), byref(total)),
+          "sampler_sizes")
+    return int(num.value), int(total.value)
+
+
+def sgd_args(lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False, maximize=False,
+             first_step=False, grad_divisor=1.0) -> SgdArgs:
+    return SgdArgs(float(lr), float(momentum), float(dampening), float(weight_decay), float(grad_divisor),
+                   int(bool(nesterov)), int(bool(maximize)), int(bool(first_step)))
+
+
+# ---- per-process default context ---------------------------------------------------
+_default: Context | None = None
+
+
+def default_context() -> Context:
+    """Created on first use for the current device and the default process group."""
+    global _default
+    if _default is None:
+        _require_cuda()
+        if dist.is_available() and dist.is_initialized():
+            rank, world = dist.get_rank(), dist.get_world_size()
+        else:
+            rank, world = 0, 1
+        if world > _lib.MAX_WORLD:
+            raise B200DDPError(f"world size {world} exceeds the single-box limit of {_lib.MAX_WORLD} GPUs")
+        ctx = Context(rank, world)
+        ctx.connect()
+        _default = ctx
+    return _default
+
+
+def reset_default_context():
+    global _default
+    if _default is not None:
+        _default.close()
+    _default = None

@@ -1,0 +1,162 @@
+/* b200ddp - C ABI of the B200-native data-parallel gradient-sync path.
+ *
+ * One process per GPU.  Plain pointers and sizes only; no torch types.  Every
+ * function returns 0 on success or a negative B200DDP_E* code and never
+ * throws; b200ddp_last_error() gives the message of the calling thread's last
+ * failure.  All device work is enqueued on the stream the caller passes; no
+ * entry point synchronises the host unless its comment says so.
+ *
+ * The reference (/root/reference, a PyTorch lab handbook) has no native code
+ * and no FFI: its interface for this path is three Python call sites.  Each
+ * group of entry points below names the reference lines it stands in for;
+ * INTEGRATION.md shows the ctypes stubs a maintainer adds to dist_utils.py.
+ */
+#ifndef B200DDP_H_
+#define B200DDP_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b200ddp_ctx b200ddp_ctx;    /* per-process, per-GPU state        */
+typedef struct b200ddp_plan b200ddp_plan;  /* bucket layout of one tensor list  */
+typedef void *b200ddp_stream;              /* a cudaStream_t                    */
+
+enum { B200DDP_F32 = 0, B200DDP_BF16 = 1 };                 /* bucket / wire dtype */
+enum { B200DDP_ALGO_AUTO = 0, B200DDP_ALGO_NCCL = 1,
+       B200DDP_ALGO_ONESHOT = 2, B200DDP_ALGO_TWOSHOT = 3 };
+enum { B200DDP_OK = 0, B200DDP_EINVAL = -1, B200DDP_ECUDA = -2, B200DDP_ENCCL = -3,
+       B200DDP_ESTATE = -4, B200DDP_ETOOBIG = -5 };
+
+#define B200DDP_MAX_WORLD 8
+#define B200DDP_IPC_BYTES 128   /* staging handle (64 B) + flag handle (64 B) */
+#define B200DDP_NCCL_UID_BYTES 128
+
+const char *b200ddp_last_error(void);
+int b200ddp_version(void);
+
+/* ---- context ---------------------------------------------------------------
+ * Replaces: dist_init / get_local_rank / get_world_size,
+ *   codes/task2/dist_utils.py:6-30 (rendezvous stays torch.distributed; this
+ *   only adds what the kernels need: peer-visible staging, flags, NCCL comm).
+ * b200ddp_create makes `device` current, allocates 2 x staging_bytes of
+ * peer-visible staging (the second half receives one-shot results) and the
+ * barrier flags; synchronises the host.
+ */
+int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200ddp_ctx **out);
+int b200ddp_destroy(b200ddp_ctx *ctx);
+int b200ddp_staging(b200ddp_ctx *ctx, void **ptr, size_t *bytes);
+int b200ddp_flags(b200ddp_ctx *ctx, void **ptr);
+
+/* NCCL baseline collective: rank 0 makes the id, every rank joins (collective). */
+int b200ddp_nccl_unique_id(void *out_uid /* B200DDP_NCCL_UID_BYTES */);
+int b200ddp_nccl_init(b200ddp_ctx *ctx, const void *uid);
+
+/* Peer memory for the P2P kernels.  Across processes: export, all-gather the
+ * handles with torch.distributed, open.  Inside one process (tests, emulation):
+ * pass the raw pointers of every rank's ctx. */
+int b200ddp_ipc_export(b200ddp_ctx *ctx, void *out /* B200DDP_IPC_BYTES */);
+int b200ddp_ipc_open_peers(b200ddp_ctx *ctx, const void *handles /* world x B200DDP_IPC_BYTES */);
+int b200ddp_set_peers_direct(b200ddp_ctx *ctx, void *const *staging_ptrs, void *const *flag_ptrs);
+
+/* ---- plan: bucket layout of a list of T fp32 tensors ------------------------
+ * Tensor t occupies bucket elements [offset[t], offset[t] + numel[t]); offsets
+ * are aligned to 32 elements, the padding stays zero.  A plan is immutable and
+ * owns the device-side chunk and pointer tables. */
+int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int bucket_dtype,
+                        b200ddp_plan **out);
+int b200ddp_plan_destroy(b200ddp_plan *plan);
+int64_t b200ddp_plan_bucket_elems(const b200ddp_plan *plan);
+int b200ddp_plan_offsets(const b200ddp_plan *plan, int64_t *out /* T */);
+
+/* ---- K1 pack + scale (+ bf16 cast) -----------------------------------------
+ * Replaces the read side of `dist.all_reduce(param.grad.data)` per parameter,
+ *   codes/task2/dist_utils.py:40-41 / codes/task3/dist_utils.py:44-45, and,
+ *   when scale = 1/world, the division at :42 / :46.
+ * bucket[offset[t] + i] = cast(grads[t][i] * scale).  `grads` is a HOST array
+ * of T device pointers to contiguous fp32 tensors. */
+int b200ddp_pack_scale(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads,
+                       void *bucket, float scale, b200ddp_stream stream);
+
+/* ---- K2 all-reduce (SUM) of a bucket that lives in this ctx's staging -------
+ * Replaces `dist.all_reduce(..., op=SUM)`, codes/task2/dist_utils.py:41.
+ * offset_bytes / nelem address the first staging half.  NCCL and two-shot
+ * reduce in place; one-shot writes its result into the second half.
+ * *result_offset_bytes receives where the sums are, relative to the staging
+ * base.  Every rank must make the same calls in the same order.  world == 1
+ * is a no-op.  bf16 buckets are summed in fp32 and rounded once. */
+int b200ddp_allreduce(b200ddp_ctx *ctx, size_t offset_bytes, int64_t nelem, int dtype, int algo,
+                      b200ddp_stream stream, size_t *result_offset_bytes);
+/* which algorithm AUTO resolves to for this size (host-only, no device work) */
+int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype);
+
+/* ---- unpack (bucket -> p.grad) ----------------------------------------------
+ * Replaces the write side of the in-place all_reduce and `param.grad.data /=
+ * world_size`, codes/task2/dist_utils.py:41-42: grads_out[t][i] =
+ * float(bucket[offset[t] + i]) / divisor (IEEE division; divisor 1 skips it). */
+int b200ddp_unpack(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket,
+                   void *const *grads_out, float divisor, b200ddp_stream stream);
+
+/* ---- K3 fused unpack + momentum-SGD -----------------------------------------
+ * Replaces `optimizer.step()` of torch.optim.SGD, codes/task2/model.py:131,62
+ *   (arithmetic: torch/optim/sgd.py:322-380), fused with the unpack above.
+ * Rounding sequence is pinned to torch's: add_(x, alpha=a) is one fma. */
+typedef struct {
+    double lr, momentum, dampening, weight_decay;
+    double grad_divisor; /* g <- g / grad_divisor before anything else; 1 = skip */
+    int nesterov, maximize;
+    int first_step;      /* momentum buffers are uninitialised: buf <- g */
+} b200ddp_sgd_args;
+
+/* gradients come from `bucket`; grads_out (nullable) also receives them, so
+ * that p.grad holds the average as it does after the reference's sync. */
+int b200ddp_unpack_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket,
+                       void *const *params, void *const *moms, void *const *grads_out,
+                       const b200ddp_sgd_args *args, b200ddp_stream stream);
+/* gradients come from T separate tensors (world == 1, or after b200ddp_unpack) */
+int b200ddp_sgd_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads,
+                     void *const *params, void *const *moms, const b200ddp_sgd_args *args,
+                     b200ddp_stream stream);
+
+/* ---- K2+K3 fused: one-shot peer reduction feeding the update directly -------
+ * Replaces codes/task2/dist_utils.py:39-42 + codes/task2/model.py:62 in one
+ * launch: every rank reads the bucket at offset_bytes from all peers' staging,
+ * sums in rank order, divides, updates.  For buckets below the one-shot
+ * crossover. */
+int b200ddp_allreduce_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, size_t offset_bytes,
+                          void *const *params, void *const *moms, void *const *grads_out,
+                          const b200ddp_sgd_args *args, b200ddp_stream stream);
+
+/* ---- single-GPU emulation of the N-rank P2P kernels (tests) -----------------
+ * Kernels of different ranks that spin on each other's flags must not be
+ * launched separately on one GPU; these run all `n` ranks' blocks as ONE
+ * cooperative launch.  ctxs[r] are contexts created on the same device with
+ * rank r / world n and linked with b200ddp_set_peers_direct. */
+int b200ddp_emu_allreduce(b200ddp_ctx *const *ctxs, int n, size_t offset_bytes, int64_t nelem,
+                          int dtype, int algo, b200ddp_stream stream, size_t *result_offset_bytes);
+int b200ddp_emu_allreduce_sgd(b200ddp_ctx *const *ctxs, b200ddp_plan *const *plans, int n,
+                              size_t offset_bytes, void *const *const *params,
+                              void *const *const *moms, void *const *const *grads_out,
+                              const b200ddp_sgd_args *args, b200ddp_stream stream);
+
+/* ---- K4 DistributedSampler index shard, built on device ----------------------
+ * Replaces `DistributedSampler(dataset, num_replicas, rank)` iteration,
+ *   codes/task2/model.py:124 (arithmetic: torch/utils/data/distributed.py:93-141
+ *   over randperm_cpu / mt19937), API shape of codes/task3/sampler.py:5-25.
+ * out_dev receives num_samples int64 indices, bit-exact with torch.
+ * n must be below 2^32/20 (torch switches to 64-bit draws there).
+ * Uses scratch owned by ctx (grown with cudaMalloc on first use of a larger n,
+ * which synchronises). */
+int b200ddp_sampler_sizes(int64_t n, int world, int drop_last, int64_t *num_samples,
+                          int64_t *total_size);
+int b200ddp_sampler_shard(b200ddp_ctx *ctx, int64_t n, int world, int rank, uint64_t seed,
+                          uint64_t epoch, int shuffle, int drop_last, int64_t *out_dev,
+                          b200ddp_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200DDP_H_ */

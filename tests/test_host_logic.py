@@ -1,0 +1,172 @@
+"""Host-side logic and CPU emulations of the device algorithms.  CPU only."""
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import b200ddp
+from b200ddp.engine import padded_numel, split_buckets
+from oracle import ref_ddp, sampler_oracle as so
+
+
+# ------------------------------------------------------------------ bucket layout
+def test_split_single_bucket_labnet():
+    out = split_buckets(ref_ddp.LABNET_NUMELS, 4, None, 1 << 20)
+    assert out == [(0, 8, 0, sum(padded_numel(n) for n in ref_ddp.LABNET_NUMELS))]
+
+
+def test_split_respects_cap_and_alignment():
+    numels = [1000, 7, 0, 5000, 33, 1]
+    out = split_buckets(numels, 4, 8192, 1 << 20)
+    assert [b[0] for b in out][0] == 0 and out[-1][1] == len(numels)
+    for (lo, hi, off, elems), nxt in zip(out, out[1:] + [None]):
+        assert off % 256 == 0
+        assert elems == sum(padded_numel(n) for n in numels[lo:hi])
+        if nxt:
+            assert nxt[0] == hi
+    # a tensor larger than the cap still gets a bucket of its own
+    assert any(hi - lo == 1 and numels[lo] == 5000 for lo, hi, _, _ in out)
+
+
+def test_split_reuses_staging_and_rejects_oversize():
+    out = split_buckets([1000] * 10, 4, 8192, 20000)
+    assert {b[2] for b in out} == {0, 8192}
+    with pytest.raises(b200ddp.B200DDPError):
+        split_buckets([10_000], 4, None, 4096)
+
+
+def test_split_bf16_halves_the_bytes():
+    a = split_buckets([4096] * 8, 4, 16384, 1 << 20)
+    b = split_buckets([4096] * 8, 2, 16384, 1 << 20)
+    assert len(a) == 8 and len(b) == 4
+
+
+# ------------------------------------------------------------------ two-shot slice partition
+@pytest.mark.parametrize("nvec,world", [(1, 2), (7, 8), (8, 8), (1000, 3), (13000, 8), (52000 // 4, 4)])
+def test_twoshot_slices_cover_bucket_once(nvec, world):
+    """csrc/p2p.cu twoshot_kernel: per = ceil(nvec / world); rank r owns [r*per, min((r+1)*per, nvec))."""
+    per = (nvec + world - 1) // world
+    seen = np.zeros(nvec, int)
+    for r in range(world):
+        lo, hi = per * r, min(per * r + per, nvec)
+        if lo < hi:
+            seen[lo:hi] += 1
+    assert (seen == 1).all()
+
+
+# ------------------------------------------------------------------ sampler: deterministic reservations
+def _reservation_shuffle(n, seed, lag=0):
+    """numpy emulation of csrc/sampler.cu: rounds of reserve (max priority =
+    lowest pending iterate) / commit.  `lag` lets a fraction of iterates run one
+    reserve phase ahead, as blocks do without a barrier after the commit."""
+    draws = so.mt19937_draws(seed, max(n - 1, 0)).astype(np.int64)
+    it = np.arange(n - 1, dtype=np.int64)
+    tgt = it + draws % (n - it)
+    perm = np.arange(n, dtype=np.int64)
+    pending = np.ones(n - 1, bool)
+    rounds = 0
+    while pending.any():
+        rounds += 1
+        idx = it[pending]
+        resv = np.full(n, n, np.int64)            # lower iterate = higher priority
+        np.minimum.at(resv, idx, idx)
+        np.minimum.at(resv, tgt[idx], idx)
+        win = (resv[idx] == idx) & (resv[tgt[idx]] == idx)
+        if lag:                                    # spurious failures must only delay, never corrupt
+            win &= (np.arange(len(idx)) % lag) != 0
+            if not win.any():
+                win[0] = True                      # the lowest pending iterate always wins on hardware too
+        w = idx[win]
+        a, b = perm[w].copy(), perm[tgt[w]].copy()
+        perm[w], perm[tgt[w]] = b, a
+        pending[w] = False
+    return perm, rounds
+
+
+@pytest.mark.parametrize("n,seed", [(2, 0), (3, 1), (10, 0), (1000, 7), (60000, 0), (50000, 3)])
+def test_reservation_shuffle_equals_sequential(n, seed):
+    perm, rounds = _reservation_shuffle(n, seed)
+    assert np.array_equal(perm, so.c_randperm(n, seed))
+    assert rounds <= 6 * max(1, int(np.log2(n))) + 8          # O(log n) dependence depth
+
+
+def test_reservation_shuffle_tolerates_spurious_failures():
+    perm, _ = _reservation_shuffle(5000, 11, lag=3)
+    assert np.array_equal(perm, so.c_randperm(5000, 11))
+
+
+def test_mt_block_parallel_recurrence():
+    """csrc/sampler.cu mt_targets: word k+624 from words k, k+1, k+397, 227 at a time."""
+    seed, ndraw = 1234, 3000
+    x = list(so.mt19937_init(seed).astype(np.uint64))
+    for base in range(0, ndraw, 227):
+        new = []
+        for k in range(base, min(base + 227, ndraw)):
+            y = (int(x[k]) & 0x80000000) | (int(x[k + 1]) & 0x7FFFFFFF)
+            new.append(int(x[k + 397]) ^ (y >> 1) ^ (0x9908B0DF if y & 1 else 0))
+        x.extend(new)                      # nothing computed in this step was read in this step
+    got = so._temper(np.asarray(x[624:624 + ndraw], np.uint32))
+    assert np.array_equal(got, so.mt19937_draws(seed, ndraw))
+
+
+# ------------------------------------------------------------------ scale policy
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 5, 8])
+def test_prescale_equals_postdivide_for_pow2(world):
+    """Power-of-two worlds pre-scale in the pack; the result must equal the
+    reference's sum-then-divide bit for bit (barring under/overflow)."""
+    rng = np.random.default_rng(world)
+    g = [(rng.standard_normal(4096) * 1e-2).astype(np.float32) for _ in range(world)]
+    post = g[0].copy()
+    for a in g[1:]:
+        post = post + a
+    post = post / np.float32(world)
+    pre = g[0] * np.float32(1.0 / world)
+    for a in g[1:]:
+        pre = pre + a * np.float32(1.0 / world)
+    if world & (world - 1) == 0:
+        assert np.array_equal(pre, post)
+    else:
+        assert np.max(np.abs(pre - post)) <= 1e-6 * np.max(np.abs(post))
+
+
+# ------------------------------------------------------------------ world_size-2 gloo run of the oracle
+def _gloo_worker(rank, ws, port, golden, q):
+    torch.set_num_threads(1)
+    ref_ddp.dist_init(ws, rank, "127.0.0.1", str(port))
+    g = dict(np.load(golden))
+    splits = np.cumsum(ref_ddp.LABNET_NUMELS)[:-1]
+    model = torch.nn.ParameterList([torch.nn.Parameter(torch.from_numpy(a.copy())) for a in np.split(g["p0"], splits)])
+    opt = torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9)
+    ok = True
+    for s in range(int(g["steps"])):
+        for p, a in zip(model, np.split(g[f"local_r{rank}_s{s}"], splits)):
+            p.grad = torch.from_numpy(a.copy())
+        ref_ddp.allreduce_average_gradients(model)
+        ok &= np.array_equal(np.concatenate([p.grad.numpy().ravel() for p in model]), g[f"avg_s{s}"])
+        opt.step()
+    ok &= np.array_equal(np.concatenate([p.detach().numpy().ravel() for p in model]), g["p_final"])
+    # sampler shards of the two ranks partition the padded permutation
+    mine = so.c_distributed_sampler_indices(1001, ws, rank, 5, 2)
+    gathered = [None] * ws
+    dist.all_gather_object(gathered, mine.tolist())
+    allidx = np.asarray(gathered).T.reshape(-1)
+    ok &= sorted(set(allidx.tolist())) == list(range(1001)) and len(allidx) == 1002
+    q.put((rank, bool(ok)))
+    dist.destroy_process_group()
+
+
+def test_oracle_under_gloo_world2(golden_dir):
+    import os
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    port = 29700 + os.getpid() % 200
+    golden = os.path.join(golden_dir, "ddp_labnet_ws2.npz")
+    procs = [ctx.Process(target=_gloo_worker, args=(r, 2, port, golden, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    res = dict(q.get() for _ in range(2))
+    assert res == {0: True, 1: True}

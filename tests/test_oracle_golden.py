@@ -1,0 +1,154 @@
+"""The oracle against the fixtures the REFERENCE produced (oracle/make_golden.py),
+and against torch itself.  CPU only."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import ref_ddp, sampler_oracle as so, synth
+
+
+def _load(golden_dir, name):
+    return dict(np.load(os.path.join(golden_dir, name)))
+
+
+# ------------------------------------------------------------------ sampler
+def test_sampler_small_golden(golden_dir):
+    g = _load(golden_dir, "sampler_small.npz")
+    assert len(g) > 1000
+    for key, ref in g.items():
+        f = dict(kv[0] == "n" and ("n", kv[1:]) or (kv[0], kv[1:]) for kv in key.split("_"))
+        n, N, d, e, s, r = (int(f[k]) for k in ("n", "N", "d", "e", "s", "r"))
+        got = so.distributed_sampler_indices(n, N, r, 3, e, bool(s), bool(d))
+        assert np.array_equal(got, ref.astype(np.int64)), key
+        assert np.array_equal(so.c_distributed_sampler_indices(n, N, r, 3, e, bool(s), bool(d)), ref.astype(np.int64)), key
+
+
+def test_sampler_reference_config_golden(golden_dir):
+    # codes/task2/model.py:124 on an MNIST-length dataset, 2 ranks
+    g = _load(golden_dir, "sampler_mnist_ws2.npz")
+    for r in range(2):
+        assert np.array_equal(so.distributed_sampler_indices(60000, 2, r), g[f"r{r}"].astype(np.int64))
+        assert np.array_equal(so.c_distributed_sampler_indices(60000, 2, r), g[f"r{r}"].astype(np.int64))
+    # SURVEY.md section 8c smoke values
+    assert g["r0"][:8].tolist() == [36044, 57327, 21567, 9481, 26145, 36531, 58716, 29792]
+    assert g["r1"][:8].tolist() == [10678, 55074, 15479, 43095, 7479, 9597, 58338, 41291]
+
+
+def test_sampler_big_golden(golden_dir):
+    g = _load(golden_dir, "sampler_big.npz")
+    keys = sorted(k[:-4] for k in g if k.endswith("_sha"))
+    assert keys
+    for key in keys:
+        parts = key.split("_")
+        n, N = int(parts[0][1:]), int(parts[1][1:])
+        seed, e, d, r = int(parts[2][4:]), int(parts[3][1:]), int(parts[4][1:]), int(parts[5][1:])
+        got = so.c_distributed_sampler_indices(n, N, r, seed, e, True, bool(d))
+        assert len(got) == int(g[key + "_len"])
+        assert np.array_equal(got[:16], g[key + "_head"]) and np.array_equal(got[-16:], g[key + "_tail"])
+        assert hashlib.sha256(got.tobytes()).digest() == bytes(g[key + "_sha"])
+
+
+@pytest.mark.parametrize("n,seed", [(0, 0), (1, 0), (2, 9), (7, 1), (625, 2), (1000, 3), (20011, 123456789),
+                                    (60000, 0), (50000, (1 << 32) + 5)])
+def test_randperm_matches_torch(n, seed):
+    ref = torch.randperm(n, generator=torch.Generator().manual_seed(seed)).numpy()
+    assert np.array_equal(so.randperm(n, seed), ref)
+    assert np.array_equal(so.c_randperm(n, seed), ref)
+
+
+def test_mt19937_known_answer():
+    # first outputs of mt19937 with the canonical default seed 5489
+    assert so.mt19937_draws(5489, 3).tolist() == [3499211612, 581869302, 3890346734]
+    # 10000th output, the value the C++ standard pins for std::mt19937
+    assert int(so.mt19937_draws(5489, 10000)[-1]) == 4123659995
+
+
+def test_sampler_rejects_bad_rank():
+    with pytest.raises(ValueError):
+        so.distributed_sampler_indices(10, 2, 2)
+
+
+# ------------------------------------------------------------------ gradient sync + update
+@pytest.mark.parametrize("ws", [2, 4])
+def test_labnet_golden_sync_and_update(golden_dir, ws):
+    """The reference's recorded local gradients, pushed through the oracle's
+    in-process average and torch.optim.SGD, reproduce what the reference's gloo
+    run produced: bit-exact at 2 ranks, rel <= 1e-5 (inf-norm) at 4."""
+    g = _load(golden_dir, f"ddp_labnet_ws{ws}.npz")
+    steps = int(g["steps"])
+    numels = ref_ddp.LABNET_NUMELS
+    splits = np.cumsum(numels)[:-1]
+    params = [torch.nn.Parameter(torch.from_numpy(a.copy())) for a in np.split(g["p0"], splits)]
+    opt = torch.optim.SGD(params, lr=0.01, momentum=0.9)
+    for s in range(steps):
+        avg = ref_ddp.average_over_ranks([torch.from_numpy(g[f"local_r{r}_s{s}"]) for r in range(ws)]).numpy()
+        if ws <= 2:
+            assert np.array_equal(avg, g[f"avg_s{s}"])
+        else:
+            assert np.max(np.abs(avg - g[f"avg_s{s}"])) <= 1e-5 * np.max(np.abs(g[f"avg_s{s}"]))
+        for p, a in zip(params, np.split(g[f"avg_s{s}"], splits)):   # the reference's own average from here on
+            p.grad = torch.from_numpy(a.copy())
+        opt.step()
+    assert np.array_equal(np.concatenate([p.detach().numpy().ravel() for p in params]), g["p_final"])
+    assert np.array_equal(np.concatenate([opt.state[p]["momentum_buffer"].numpy().ravel() for p in params]), g["m_final"])
+
+
+GRID_CASES = [("A", 1), ("A", 2), ("A", 4), ("A", 8), ("B", 2), ("C", 2), ("D", 2)]
+
+
+@pytest.mark.parametrize("variant,ws", GRID_CASES)
+def test_grid_golden_numpy_restatement(golden_dir, variant, ws):
+    """sgd_step_numpy + average_over_ranks against the reference run on injected
+    grid gradients: exact at every world size (sums are order-independent)."""
+    g = _load(golden_dir, f"ddp_grid_{variant}_ws{ws}.npz")
+    hp = synth.SGD_VARIANTS[variant]
+    p = [synth.init_param(n, t) for t, n in enumerate(synth.RAGGED_NUMELS)]
+    buf = [None] * len(p)
+    avg = None
+    for s in range(int(g["steps"])):
+        avg = []
+        for t, n in enumerate(synth.RAGGED_NUMELS):
+            a = ref_ddp.average_over_ranks([torch.from_numpy(synth.grid_grad(n, r, s, t)) for r in range(ws)]).numpy()
+            p[t], buf[t] = ref_ddp.sgd_step_numpy(p[t], a, buf[t], **hp)
+            avg.append(a)
+    assert np.array_equal(np.concatenate(avg), g["avg"])
+    assert np.array_equal(np.concatenate(p), g["p"])
+    if "m" in g:
+        assert np.array_equal(np.concatenate(buf), g["m"])
+
+
+@pytest.mark.parametrize("ws", [4, 8])
+def test_dense_golden_tolerance(golden_dir, ws):
+    """Full-mantissa gradients at 4 / 8 ranks: rank-order summation vs gloo's
+    order stays within the stated fp32 bound, rel <= 1e-5 (inf-norm)."""
+    g = _load(golden_dir, f"ddp_dense_A_ws{ws}.npz")
+    s = int(g["steps"]) - 1
+    avg = np.concatenate([ref_ddp.average_over_ranks(
+        [torch.from_numpy(synth.dense_grad(n, r, s, t)) for r in range(ws)]).numpy()
+        for t, n in enumerate(synth.RAGGED_NUMELS)])
+    assert np.max(np.abs(avg - g["avg"])) <= 1e-5 * np.max(np.abs(g["avg"]))
+
+
+def test_numpy_sgd_equals_torch_sgd():
+    rng = np.random.default_rng(0)
+    for hp in synth.SGD_VARIANTS.values():
+        p0 = rng.standard_normal(1000).astype(np.float32)
+        tp = torch.nn.Parameter(torch.from_numpy(p0.copy()))
+        opt = torch.optim.SGD([tp], **hp)
+        p, buf = p0, None
+        for _ in range(4):
+            gr = (rng.standard_normal(1000) * 1e-2).astype(np.float32)
+            tp.grad = torch.from_numpy(gr.copy())
+            opt.step()
+            p, buf = ref_ddp.sgd_step_numpy(p, gr, buf, **hp)
+        assert np.array_equal(p, tp.detach().numpy())
+
+
+def test_labnet_shape():
+    m = ref_ddp.LabNet()
+    assert tuple(p.numel() for p in m.parameters()) == ref_ddp.LABNET_NUMELS
+    assert sum(ref_ddp.LABNET_NUMELS) == 51902
+    assert m(torch.zeros(2, 1, 28, 28)).shape == (2, 10)
