@@ -1,0 +1,466 @@
+#!/usr/bin/env python
+"""bench.py - the reference's headline workload on N GPUs of one box.
+
+    python bench.py --gpus N --steps K --warmup W                 # this repo's path
+    python bench.py --impl reference --gpus N --steps K --warmup W  # reference's CPU path (gloo)
+
+Workload (BASELINE.json configs[1]): the task3 training loop - ResNet-18
+(10 classes) on CIFAR-10-shaped synthetic data, 128 samples per rank, fp32,
+SGD(lr=0.001, momentum=0.9) (codes/task3/model.py:118), one process per GPU.
+A step is the reference's hot loop body (codes/task2/model.py:49-63):
+forward, backward, gradient sync, optimizer step.  Forward/backward stay
+torch/cuDNN (they are not on the path this repo replaces); the sync and the
+update run on libb200ddp.so.
+
+One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every key.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+MODELS = {
+    # name: (ctor key for oracle.ref_ddp.build_model, per-rank batch, lr)
+    "labnet": ("labnet", 32, 0.01),        # configs[0]: codes/task2/model.py:126,131
+    "resnet18": ("resnet18", 128, 0.001),  # configs[1]: codes/task3/model.py:118
+    "resnet50": ("resnet50", 256, 0.001),  # configs[2]
+}
+METRIC = "train samples/sec"
+UNIT = "samples/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=30)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--model", default="resnet18", choices=sorted(MODELS))
+    ap.add_argument("--batch", type=int, default=0, help="per-rank batch (0 = the config's)")
+    ap.add_argument("--bucket-dtype", default=None, choices=["fp32", "bf16"])
+    ap.add_argument("--algo", default="auto", choices=["auto", "nccl", "oneshot", "twoshot"])
+    ap.add_argument("--mode", default="fused", choices=["fused", "strict"],
+                    help="fused: sync folded into optimizer.step(); strict: p.grad averaged first")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--cpu-budget-s", type=float, default=15.0)
+    return ap.parse_args()
+
+
+def env_int(name, default):
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+# --------------------------------------------------------------------------- models (host side, shared by both arms)
+def build_model(name):
+    import torch
+    torch.manual_seed(0)             # every rank builds identical weights and BN buffers
+    if name == "labnet":
+        import torch.nn as nn
+
+        class LabCNN(nn.Module):     # layer shapes of `Net`, codes/task2/model.py:13-37
+            def __init__(self):
+                super().__init__()
+                self.conv1 = nn.Conv2d(1, 6, 5, 1, 2)
+                self.conv2 = nn.Conv2d(6, 16, 5, 1, 0)
+                self.fc1 = nn.Linear(400, 120)
+                self.fc2 = nn.Linear(120, 10)
+
+            def forward(self, x):
+                f = nn.functional
+                x = f.max_pool2d(f.relu(self.conv1(x)), 2)
+                x = f.max_pool2d(f.relu(self.conv2(x)), 2)
+                return self.fc2(f.relu(self.fc1(x.flatten(1))))
+        return LabCNN(), (1, 28, 28), 10
+    import torchvision
+    if name == "resnet18":
+        return torchvision.models.resnet18(num_classes=10), (3, 32, 32), 10
+    return torchvision.models.resnet50(), (3, 224, 224), 1000
+
+
+def make_batches(rank, count, batch, chw, classes, pin):
+    import torch
+    g = torch.Generator().manual_seed(1234 + rank)
+    out = []
+    for _ in range(count):
+        x = torch.rand((batch,) + tuple(chw), generator=g)
+        y = torch.randint(0, classes, (batch,), generator=g)
+        if pin:
+            x, y = x.pin_memory(), y.pin_memory()
+        out.append((x, y))
+    return out
+
+
+# --------------------------------------------------------------------------- clocks
+class ClockSampler:
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.lines, self.proc = [], None
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._pump, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ln in self.lines:
+            f = [c.strip() for c in ln.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); power.append(float(f[2]))
+            except ValueError:
+                continue
+            for nm, v in zip(names, f[3:7]):
+                if v == "Active":
+                    reasons.add(nm)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# --------------------------------------------------------------------------- CPU arm (oracle port of the reference)
+def _cpu_worker(rank, world, port, model_name, batch, lr, steps, warmup, threads, q):
+    """The reference's own path on host cores: its dist_utils functions as
+    restated in oracle/ref_ddp.py (gloo), torch.optim.SGD, CPU tensors."""
+    import torch
+    from oracle import ref_ddp
+    torch.set_num_threads(threads)
+    if world > 1:
+        ref_ddp.dist_init(world, rank, "127.0.0.1", str(port))
+    model, chw, classes = build_model(model_name)
+    opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=0.9)
+    loss_fn = torch.nn.CrossEntropyLoss()
+    model.train()
+    ref_ddp.init_parameters(model)
+    data = make_batches(rank, 4, batch, chw, classes, pin=False)
+
+    def step(i):
+        x, y = data[i % len(data)]
+        loss = loss_fn(model(x), y)
+        opt.zero_grad()
+        loss.backward()
+        ref_ddp.allreduce_average_gradients(model) if world > 1 else None   # one rank: all_reduce + /1 is the identity
+        opt.step()
+        return float(loss)
+
+    for i in range(warmup):
+        step(i)
+    if world > 1:
+        torch.distributed.barrier()
+    t0 = time.perf_counter()
+    for i in range(steps):
+        step(i)
+    if world > 1:
+        torch.distributed.barrier()
+    dt = time.perf_counter() - t0
+    if rank == 0:
+        q.put(dt)
+    if world > 1:
+        torch.distributed.destroy_process_group()
+
+
+def run_cpu(world, model_name, batch, lr, steps, warmup):
+    """Returns seconds for `steps` steps (max over ranks is rank 0's barrier-fenced time)."""
+    import torch.multiprocessing as mp
+    cores = len(os.sched_getaffinity(0))
+    threads = max(1, cores // world)
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    port = 29800 + os.getpid() % 150
+    procs = [ctx.Process(target=_cpu_worker, args=(r, world, port, model_name, batch, lr, steps, warmup, threads, q))
+             for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join()
+        if p.exitcode != 0:
+            raise RuntimeError(f"CPU worker exited with {p.exitcode}")
+    return q.get(), cores, threads
+
+
+def cpu_sample(world, model_name, batch, lr, budget_s):
+    """A bounded sample of the workload on the host cores: probe one step, then
+    as many steps (and as large a per-rank batch) as fit the budget."""
+    probe_batch = min(batch, 32)
+    dt, cores, threads = run_cpu(world, model_name, probe_batch, lr, 1, 1)
+    per_sample = dt / probe_batch
+    b = batch
+    while b > 8 and per_sample * b * 3 > budget_s:
+        b //= 2
+    steps = max(2, min(20, int(budget_s / max(per_sample * b, 1e-6))))
+    dt, cores, threads = run_cpu(world, model_name, b, lr, steps, 1)
+    return {"value": world * b * steps / dt, "unit": UNIT, "cores": threads * world, "kind": "port",
+            "sample": f"{steps} steps x {b} samples/rank x {world} rank(s), {threads} thread(s)/rank of {cores} cores, "
+                      f"after 1 warm-up step (full batch is {batch}/rank)",
+            "ms_per_step": dt / steps * 1e3, "batch": b, "steps": steps}
+
+
+def reference_arm(args):
+    """bench.py --impl reference: the reference's CPU implementation of the path
+    (oracle port: /root/reference is pure Python and does not travel)."""
+    rank = env_int("RANK", 0)
+    if rank != 0:
+        return 0                     # rank 0 alone runs the N-process gloo job on the host cores
+    name, batch, lr = MODELS[args.model]
+    batch = args.batch or batch
+    world = args.gpus
+    probe_batch = min(batch, 32)
+    dt, cores, threads = run_cpu(world, name, probe_batch, lr, 1, 1)
+    per_sample = dt / probe_batch
+    budget = 150.0
+    b = batch
+    while b > 8 and per_sample * b * (args.steps + args.warmup) > budget:
+        b //= 2
+    dt, cores, threads = run_cpu(world, name, b, lr, args.steps, args.warmup)
+    value = world * b * args.steps / dt
+    sample = (f"{args.steps} steps x {b} samples/rank x {world} gloo rank(s), {threads} thread(s)/rank of {cores} cores"
+              f" (full batch is {batch}/rank)")
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.model, batch, world, "cpu-gloo", None),
+            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads * world, "kind": "port", "sample": sample},
+            "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(model, batch, world, parallelism, extra):
+    cfg = {"workload": {"labnet": "task2 lab CNN on MNIST-shaped synthetic data (1x28x28)",
+                        "resnet18": "task3 DDP loop: ResNet-18 (10 classes) on CIFAR-10-shaped synthetic data (3x32x32)",
+                        "resnet50": "ResNet-50 on ImageNet-shaped synthetic data (3x224x224)"}[model],
+           "batch_per_rank": batch, "global_batch": batch * world, "optimizer": "SGD momentum 0.9",
+           "parallelism": f"{parallelism}{world}" if parallelism != "cpu-gloo" else f"gloo x{world} on CPU"}
+    if extra:
+        cfg.update(extra)
+    return cfg
+
+
+# --------------------------------------------------------------------------- GPU arm
+def flush_l2(buf):
+    buf.add_(1.0)          # 512 MB read-modify-write: evicts the 126 MB L2
+
+
+def kernel_microbench(ctx, params, moms, grads, peak_gbs, iters=20):
+    """pack / update in isolation on this model's tensor list, L2 flushed between
+    timed launches, CUDA events on the launching stream."""
+    import torch
+    import b200ddp
+    numels = [p.numel() for p in params]
+    P = sum(numels)
+    res = {}
+    flush = torch.empty(128 << 20, dtype=torch.float32, device=params[0].device)
+    plan = ctx.plan(numels)
+    if plan.bucket_bytes > ctx.staging_bytes:
+        return res
+    gp, pp, mp_ = [g.data_ptr() for g in grads], [p.data_ptr() for p in params], [m.data_ptr() for m in moms]
+    hp = b200ddp.sgd_args(lr=0.0, momentum=1.0)      # lr 0, momentum 1: leaves params untouched, m += g
+
+    def time_it(fn, nbytes):
+        ts = []
+        for _ in range(iters + 3):
+            flush_l2(flush)
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record(); fn(); b.record()
+            b.synchronize()
+            ts.append(a.elapsed_time(b) * 1e-3)
+        ts = ts[3:]
+        t = statistics.median(ts)
+        return {"us": t * 1e6, "gbs": nbytes / t / 1e9, "frac_of_measured_hbm": nbytes / t / 1e9 / peak_gbs}
+
+    res["pack_fp32"] = time_it(lambda: ctx.pack_scale(plan, gp, ctx.bucket_ptr(0), 0.5), 8 * P)
+    res["update_direct"] = time_it(lambda: ctx.sgd_step(plan, gp, pp, mp_, hp), 20 * P)
+    res["update_from_bucket_write_grad"] = time_it(
+        lambda: ctx.unpack_sgd(plan, ctx.bucket_ptr(0), pp, mp_, gp, hp), 24 * P)
+    plan16 = ctx.plan(numels, "bf16")
+    res["pack_bf16"] = time_it(lambda: ctx.pack_scale(plan16, gp, ctx.bucket_ptr(0), 0.5), 6 * P)
+    res["update_from_bf16_bucket"] = time_it(lambda: ctx.unpack_sgd(plan16, ctx.bucket_ptr(0), pp, mp_, None, hp), 18 * P)
+    plan.close(); plan16.close()
+    return res
+
+
+def gpu_arm(args):
+    import torch
+    import torch.distributed as dist
+
+    import b200ddp
+
+    world = env_int("WORLD_SIZE", 1)
+    rank = env_int("RANK", 0)
+    local = env_int("LOCAL_RANK", 0)
+    if world != args.gpus and world > 1:
+        raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
+    if args.gpus > 1 and world == 1:
+        raise SystemExit("launch multi-GPU runs with torch.distributed.run (one rank per GPU)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    name, batch, lr = MODELS[args.model]
+    batch = args.batch or batch
+    bucket_dtype = args.bucket_dtype or ("bf16" if args.model == "resnet50" else "fp32")
+    b200ddp.configure(bucket_dtype=bucket_dtype, algo=args.algo)
+
+    model, chw, classes = build_model(name)
+    model = model.to(dev).train()
+    b200ddp.init_parameters(model)
+    opt = b200ddp.SGD(model.parameters(), lr=lr, momentum=0.9)
+    if args.mode == "fused":
+        b200ddp.enable_fused_step(model, opt)
+    loss_fn = torch.nn.CrossEntropyLoss()
+    params = list(model.parameters())
+    P = sum(p.numel() for p in params)
+    host_batches = make_batches(rank, 8, batch, chw, classes, pin=True)
+    dev_batches = [(x.to(dev), y.to(dev)) for x, y in host_batches]
+    h2d = host_batches[0][0].numel() * 4 + host_batches[0][1].numel() * 8
+    k3 = []                      # (start, end) events around our sync+update kernels, per timed step
+
+    def step(i, e2e, record=False):
+        if e2e:
+            x, y = host_batches[i % 8]
+            x, y = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
+        else:
+            x, y = dev_batches[i % 8]
+        loss = loss_fn(model(x), y)
+        opt.zero_grad()
+        loss.backward()
+        if record:
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+        b200ddp.allreduce_average_gradients(model)
+        opt.step()
+        if record:
+            b.record()
+            k3.append((a, b))
+        return loss.item() if e2e else loss      # e2e reads the loss back every step (codes/task2/model.py:63)
+
+    def fence():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(e2e, steps, record=False):
+        fence()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(steps):
+            step(i, e2e, record)
+        b.record()
+        fence()
+        t = torch.tensor([a.elapsed_time(b) * 1e-3], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for i in range(max(args.warmup, 3)):
+        step(i, False)
+    eng = b200ddp.dist_utils.engine_for(model)
+    launches0 = opt.launches + (eng.launches if args.mode == "strict" else 0)
+    clocks = ClockSampler(local) if rank == 0 else None
+    t_dev = timed(False, args.steps, record=True)
+    launches = opt.launches + (eng.launches if args.mode == "strict" else 0) - launches0
+    for i in range(3):
+        step(i, True)
+    t_e2e = timed(True, args.steps)
+    clk = clocks.stop() if clocks else None
+    ours_s = statistics.mean(a.elapsed_time(b) for a, b in k3) * 1e-3
+
+    # ---- the dominant kernel of ours, against the measured HBM peak
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except (OSError, ValueError):
+        pass
+    peak_gbs, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
+    extras = {}
+    if rank == 0:
+        ctx = b200ddp.default_context()
+        moms = [opt.state[p]["momentum_buffer"] for p in params]
+        grads = [p.grad for p in params]
+        try:
+            extras["kernels"] = kernel_microbench(ctx, params, moms, grads, peak_gbs)
+        except b200ddp.B200DDPError as e:      # e.g. model larger than the staging area
+            extras["kernels_error"] = str(e)
+    if world > 1:
+        dist.barrier()
+    bytes_per_elem = 20 if world == 1 else (24 if bucket_dtype == "fp32" else 22)
+    kern = extras.get("kernels", {}).get("update_direct" if world == 1 else
+                                         ("update_from_bucket_write_grad" if bucket_dtype == "fp32" else "update_from_bf16_bucket"))
+    traffic = None
+    try:
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "update_kernel_traffic.json"))).get(args.model)
+    except (OSError, ValueError):
+        pass
+    roofline = None
+    if kern:
+        roofline = {"bound": "hbm", "kernel": "update_kernel (K3 unpack + momentum-SGD)",
+                    "achieved": kern["gbs"], "peak": peak_gbs, "peak_source": peak_src, "unit": "GB/s",
+                    "frac": kern["gbs"] / peak_gbs, "traffic": traffic,
+                    "algorithmic_bytes_per_launch": bytes_per_elem * P if world > 1 else 20 * P,
+                    "launch_us": kern["us"], "how": "CUDA events around single launches, L2 flushed between them",
+                    "in_step_sync_plus_update_us": ours_s * 1e6}
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return 0
+    line = {"metric": METRIC, "value": world * batch * args.steps / t_dev, "unit": UNIT, "n_gpus": world,
+            "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": t_dev / args.steps * 1e3,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(args.model, batch, world, "dp", {
+                "params": P, "tensors": len(params), "bucket_dtype": bucket_dtype, "mode": args.mode, "algo": args.algo,
+                "l2": "step working set (params+momentum+grads = %.0f MB plus activations) exceeds the 126 MB L2; "
+                      "kernel micro-benchmarks flush L2 between launches" % (12 * P / 1e6)}),
+            "e2e": {"value": world * batch * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": 4, "ms_per_step": t_e2e / args.steps * 1e3},
+            "gpu_launches": launches, "clocks": clk, "roofline": roofline,
+            "sync_update_ms_per_step": ours_s * 1e3}
+    line.update(extras)
+    if world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_sample(1, name, batch, lr, args.cpu_budget_s)
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        return reference_arm(args)
+    return gpu_arm(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

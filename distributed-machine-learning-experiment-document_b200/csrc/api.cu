@@ -163,6 +163,7 @@ int b200ddp_destroy(b200ddp_ctx *ctx) {
     cudaFree(ctx->sampler_scratch);
     cudaFree(ctx->staging);
     cudaFree(ctx->flags);
+    cudaGetLastError();
     delete ctx;
     return B200DDP_OK;
 }
@@ -265,6 +266,7 @@ int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int buck
     b200ddp_plan *p = new (std::nothrow) b200ddp_plan();
     B2_REQUIRE(p != nullptr, B200DDP_ESTATE, "out of host memory");
     p->ctx = ctx;
+    p->device = ctx->device;
     p->T = T;
     p->dtype = bucket_dtype;
     int64_t off = 0;
@@ -311,7 +313,9 @@ int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int buck
 
 int b200ddp_plan_destroy(b200ddp_plan *p) {
     if (!p) return B200DDP_OK;
-    if (p->ctx) cudaSetDevice(p->ctx->device);
+    int prev = -1;
+    cudaGetDevice(&prev);
+    cudaSetDevice(p->device);
     for (int i = 0; i < b200ddp_plan::kRing; ++i) {
         if (p->pinned_ev[i]) {
             cudaEventSynchronize(p->pinned_ev[i]);
@@ -322,6 +326,8 @@ int b200ddp_plan_destroy(b200ddp_plan *p) {
     cudaFree(p->d_meta);
     cudaFree(p->d_chunks);
     cudaFree(p->d_ptrs);
+    if (prev >= 0) cudaSetDevice(prev);
+    cudaGetLastError();   // teardown never leaves a stale error behind for the next launch check
     delete p;
     return B200DDP_OK;
 }

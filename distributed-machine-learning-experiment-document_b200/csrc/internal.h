@@ -88,7 +88,8 @@ struct b200ddp_ctx {
 };
 
 struct b200ddp_plan {
-    b200ddp_ctx *ctx = nullptr;
+    b200ddp_ctx *ctx = nullptr;        // identity check only; never dereferenced after creation
+    int device = 0;
     int T = 0;
     int dtype = B200DDP_F32;
     int64_t bucket_elems = 0;

@@ -323,6 +323,7 @@ int launch_oneshot_update(b200ddp_ctx *ctx, const PlanView &pv, int dtype, size_
     PlanSet<false> ps;
     ps.v[0] = pv;
     const int grid = update_grid(pv.nchunks);
+    cudaGetLastError();
 #define B2_FUSED(BT, WG) oneshot_update_kernel<BT, WG, false><<<grid, kThreads, 0, s>>>(a, ps, hp)
     if (dtype == B200DDP_F32) {
         if (write_grad) B2_FUSED(float, true); else B2_FUSED(float, false);

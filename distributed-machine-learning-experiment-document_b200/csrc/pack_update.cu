@@ -193,6 +193,7 @@ template <typename K> int grid_for(K kernel, int nchunks, int sm_count) {
 
 int launch_pack(const PlanView &pv, int dtype, void *bucket, float scale, int sm_count, cudaStream_t s) {
     if (pv.nchunks == 0) return B200DDP_OK;
+    cudaGetLastError();   // a stale error of an unrelated earlier call must not be blamed on this launch
     if (dtype == B200DDP_F32) {
         pack_kernel<float><<<grid_for(pack_kernel<float>, pv.nchunks, sm_count), kThreads, 0, s>>>(pv, (float *)bucket,
                                                                                                   scale);
@@ -206,6 +207,7 @@ int launch_pack(const PlanView &pv, int dtype, void *bucket, float scale, int sm
 
 int launch_unpack(const PlanView &pv, int dtype, const void *bucket, float divisor, int sm_count, cudaStream_t s) {
     if (pv.nchunks == 0) return B200DDP_OK;
+    cudaGetLastError();
     const int use_div = divisor != 1.0f;
     if (dtype == B200DDP_F32) {
         unpack_kernel<float><<<grid_for(unpack_kernel<float>, pv.nchunks, sm_count), kThreads, 0, s>>>(
@@ -221,6 +223,7 @@ int launch_unpack(const PlanView &pv, int dtype, const void *bucket, float divis
 int launch_update(const PlanView &pv, int dtype, const void *bucket, bool write_grad, const SgdScalars &hp,
                   int sm_count, cudaStream_t s) {
     if (pv.nchunks == 0) return B200DDP_OK;
+    cudaGetLastError();
 #define B2_UPD(BT, FB, WG)                                                                              \
     update_kernel<BT, FB, WG><<<grid_for(update_kernel<BT, FB, WG>, pv.nchunks, sm_count), kThreads, 0, s>>>( \
         pv, (const BT *)bucket, hp)

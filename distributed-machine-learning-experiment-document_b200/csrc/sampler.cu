@@ -204,6 +204,7 @@ int launch_sampler(b200ddp_ctx *ctx, int64_t n, int world, int rank, uint64_t se
     if (!shuffle) {
         int grid = (int)((num_samples + 255) / 256);
         if (grid > 4 * ctx->sm_count) grid = 4 * ctx->sm_count;
+        cudaGetLastError();
         sampler_sequential_kernel<<<grid, 256, 0, s>>>(n, world, rank, num_samples, out_dev);
         B2_CHECK_CUDA(cudaGetLastError());
         return B200DDP_OK;

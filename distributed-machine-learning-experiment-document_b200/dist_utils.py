@@ -80,7 +80,9 @@ def allreduce_average_gradients(model):
     over ranks.  With enable_fused_step(model, optimizer) the work is deferred
     to optimizer.step(), which then also leaves the mean in p.grad."""
     eng = engine_for(model)
-    if getattr(eng, "fused_optimizer", None) is not None:
+    if eng.fused_optimizer is not None and eng.fused_optimizer() is None:
+        eng.fused_optimizer = None        # the optimizer it was fused with is gone: back to the strict path
+    if eng.fused_optimizer is not None:
         for p in eng.params:
             if p.grad is None:
                 raise AttributeError("'NoneType' object has no attribute 'data'")

@@ -10,6 +10,7 @@ from __future__ import annotations
 
 import ctypes
 import os
+import weakref
 from ctypes import byref, c_int64, c_size_t, c_void_p
 
 import torch
@@ -60,6 +61,7 @@ class Plan:
         check(_lib.lib().b200ddp_plan_offsets(h, offs), "plan_offsets")
         self.offsets = list(offs)[: self.T]
         self.bucket_bytes = self.bucket_elems * self.esize
+        ctx._plans.add(self)
 
     def close(self):
         if getattr(self, "handle", None):
@@ -94,6 +96,7 @@ class Context:
         self.flags_ptr = int(f.value)
         self.has_nccl = False
         self.has_peers = self.world == 1
+        self._plans = weakref.WeakSet()
 
     # ---- set-up --------------------------------------------------------------
     def connect(self, group=None, nccl=True, p2p=True):
@@ -130,6 +133,8 @@ class Context:
 
     def close(self):
         if getattr(self, "handle", None):
+            for pl in list(self._plans):
+                pl.close()
             _lib.lib().b200ddp_destroy(self.handle)
             self.handle = None
 
