@@ -63,7 +63,10 @@ _SIGNATURES = {
     "b200ddp_sampler_sizes": (c_int, [c_int64, c_int, c_int, POINTER(c_int64), POINTER(c_int64)]),
     "b200ddp_sampler_shard": (c_int, [c_void_p, c_int64, c_int, c_int, c_uint64, c_uint64, c_int, c_int,
                                       c_void_p, c_void_p]),
+    "b200ddp_sampler_shard_static": (c_int, [c_int64, c_int, c_int, c_uint64, c_uint64, c_int, c_int,
+                                             c_void_p, c_void_p]),
 }
+SAMPLER_STATIC_MAX_N = 65536
 
 _lib = None
 

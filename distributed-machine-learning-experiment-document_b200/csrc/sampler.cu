@@ -223,3 +223,103 @@ int launch_sampler(b200ddp_ctx *ctx, int64_t n, int world, int rank, uint64_t se
 }
 
 }  // namespace b200ddp
+
+// =====================================================================================
+// b200ddp_sampler_shard_static: the same shard, for callers that must not allocate.
+//
+// Who that is: a host program that has already handed the GPU's memory to its own
+// pool (any further cudaMalloc would fail, or take memory the pool counts on), and
+// a loop that cannot afford cudaMalloc's device-wide stall - e.g. refilling the
+// sampler for the next epoch while training kernels of other streams are running.
+// The regular entry point needs a context (which allocates staging) and grows its
+// scratch with cudaMalloc; this one needs neither.
+//
+// Its scratch (swap targets, permutation, reservation words, round counters, the
+// grid-barrier counter) lives in the fixed array below, which every GPU that loads
+// the library carries until the process exits.  Limits and rules for the caller:
+//   * n <= B200DDP_SAMPLER_STATIC_MAX_N (65,536: MNIST's 60,000 and CIFAR's 50,000
+//     fit); a larger n is refused with B200DDP_ETOOBIG, never truncated.
+//   * The first call on each device looks up the array's device address
+//     (cudaGetSymbolAddress) and the SM count.  Make that first call outside any
+//     stream capture.
+//   * All calls on one device share the one array.  Nothing a previous call left in
+//     it is relied on: the kernel rewrites targets and permutation and zeroes the
+//     reservation words and round counters itself, and the barrier counter is
+//     cleared on the stream just before the launch.  Two calls on one device whose
+//     kernels overlap in time (issued on different streams with no ordering between
+//     them) race on the array and corrupt each other: issue them on one stream, or
+//     order the streams yourself.  Another process has its own copy of the array.
+//   * No cudaMalloc / cudaFree / allocating library call is made, here or below.
+// =====================================================================================
+namespace {
+
+constexpr int64_t kStaticMaxN = B200DDP_SAMPLER_STATIC_MAX_N;
+constexpr size_t kStaticScratchBytes =
+    ((size_t)kStaticMaxN * 8 + 255) / 256 * 256 + 2 * (((size_t)kStaticMaxN * 4 + 255) / 256 * 256) +
+    ((size_t)b200ddp::kMaxRounds * 4 + 255) / 256 * 256 + 256;
+
+// Device storage.  In host code this name is only a handle for the runtime's symbol
+// table - it is NOT a device address and must never be passed to a kernel as one.
+static __device__ __align__(256) unsigned char g_static_sampler_scratch[kStaticScratchBytes];
+
+constexpr int kMaxDevices = 64;
+struct StaticSlot {
+    void *scratch = nullptr;   // device address of g_static_sampler_scratch on this device
+    int sm_count = 0;
+};
+StaticSlot g_static_slots[kMaxDevices];
+std::mutex g_static_mu;
+
+// Once per device, with that device current.
+int static_slot_for_current_device(StaticSlot *out) {
+    int dev = -1;
+    B2_CHECK_CUDA(cudaGetDevice(&dev));
+    B2_REQUIRE(dev >= 0 && dev < kMaxDevices, B200DDP_EINVAL, "device ordinal %d outside [0, %d)", dev, kMaxDevices);
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    StaticSlot &slot = g_static_slots[dev];
+    if (slot.scratch == nullptr) {
+        void *ptr = nullptr;
+        B2_CHECK_CUDA(cudaGetSymbolAddress(&ptr, g_static_sampler_scratch));
+        B2_REQUIRE(ptr != nullptr, B200DDP_ECUDA, "cudaGetSymbolAddress returned a null address");
+        int sms = 0;
+        B2_CHECK_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+        B2_REQUIRE(sms > 0, B200DDP_ECUDA, "device %d reports %d SMs", dev, sms);
+        slot.sm_count = sms;
+        slot.scratch = ptr;
+    }
+    *out = slot;
+    return B200DDP_OK;
+}
+
+}  // namespace
+
+extern "C" int b200ddp_sampler_shard_static(int64_t n, int world, int rank, uint64_t seed, uint64_t epoch,
+                                            int shuffle, int drop_last, int64_t *out_dev, b200ddp_stream stream) {
+    using namespace b200ddp;
+    B2_REQUIRE(world >= 1, B200DDP_EINVAL, "num_replicas must be positive");
+    B2_REQUIRE(rank >= 0 && rank < world, B200DDP_EINVAL, "Invalid rank %d, rank should be in the interval [0, %d]",
+               rank, world - 1);
+    B2_REQUIRE(n >= 0, B200DDP_EINVAL, "negative dataset length");
+    B2_REQUIRE(n <= kStaticMaxN, B200DDP_ETOOBIG,
+               "dataset length %lld exceeds the %lld indices the allocation-free sampler has room for; "
+               "use b200ddp_sampler_shard",
+               (long long)n, (long long)kStaticMaxN);
+    int64_t num = 0;
+    if (int rc = b200ddp_sampler_sizes(n, world, drop_last, &num, nullptr)) return rc;
+    if (num <= 0 || n == 0) return B200DDP_OK;
+    B2_REQUIRE(out_dev != nullptr, B200DDP_EINVAL, "out_dev is NULL");
+    B2_REQUIRE(sampler_scratch_bytes(n) <= kStaticScratchBytes, B200DDP_ETOOBIG, "static scratch too small for n=%lld",
+               (long long)n);
+    StaticSlot slot;
+    if (int rc = static_slot_for_current_device(&slot)) return rc;
+    cudaStream_t s = (cudaStream_t)stream;
+    if (!shuffle) {
+        int grid = (int)((num + 255) / 256);
+        if (grid > 4 * slot.sm_count) grid = 4 * slot.sm_count;
+        cudaGetLastError();
+        sampler_sequential_kernel<<<grid, 256, 0, s>>>(n, world, rank, num, out_dev);
+        B2_CHECK_CUDA(cudaGetLastError());
+        return B200DDP_OK;
+    }
+    return launch_sampler_on(slot.scratch, slot.sm_count, n, world, rank, seed + epoch, num, out_dev, s);
+}

@@ -211,6 +211,27 @@ def sampler_sizes(n: int, world: int, drop_last: bool) -> tuple[int, int]:
     return int(num.value), int(total.value)
 
 
+def sampler_shard_static(out: torch.Tensor, n, world, rank, seed=0, epoch=0, shuffle=True, drop_last=False,
+                         stream=None) -> torch.Tensor:
+    """Allocation-free sampler shard (b200ddp_sampler_shard_static): fills the
+    caller's int64 CUDA tensor `out` (at least num_samples long, on the current
+    device) and returns the filled prefix.  For callers that cannot let the
+    library allocate - see include/b200ddp.h.  n is limited to
+    _lib.SAMPLER_STATIC_MAX_N; all calls on a device share one scratch array, so
+    keep them on one stream."""
+    _require_cuda()
+    num = sampler_sizes(n, world, drop_last)[0]
+    fits = n <= _lib.SAMPLER_STATIC_MAX_N     # beyond the limit the library's own refusal is the error to show
+    if fits and (out.dtype != torch.int64 or not out.is_cuda or not out.is_contiguous() or out.numel() < max(num, 0)):
+        raise B200DDPError(f"out must be a contiguous int64 CUDA tensor with at least {num} elements")
+    check(_lib.lib().b200ddp_sampler_shard_static(int(n), int(world), int(rank), int(seed) & 0xFFFFFFFFFFFFFFFF,
+                                                  int(epoch) & 0xFFFFFFFFFFFFFFFF, int(bool(shuffle)),
+                                                  int(bool(drop_last)),
+                                                  c_void_p(out.data_ptr()) if fits and num > 0 else None,
+                                                  _stream_handle(stream)), "sampler_shard_static")
+    return out[: max(num, 0)]
+
+
 def sgd_args(lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False, maximize=False,
              first_step=False, grad_divisor=1.0) -> SgdArgs:
     return SgdArgs(float(lr), float(momentum), float(dampening), float(weight_decay), float(grad_divisor),

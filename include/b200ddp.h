@@ -156,6 +156,24 @@ int b200ddp_sampler_shard(b200ddp_ctx *ctx, int64_t n, int world, int rank, uint
                           uint64_t epoch, int shuffle, int drop_last, int64_t *out_dev,
                           b200ddp_stream stream);
 
+/* ---- allocation-free variant of the sampler shard ----------------------------
+ * No counterpart in the reference (its sampler is host Python); added for
+ * callers that must not allocate device memory: a host program whose own pool
+ * already owns the GPU's memory, or a loop that cannot take cudaMalloc's
+ * device-wide stall (say, refilling next epoch's indices while other streams
+ * train).  Needs no context.  Same output as b200ddp_sampler_shard, written to
+ * the caller's out_dev, on the CURRENT device and the given stream.
+ * Scratch is a fixed array inside the library (about 1 MiB per GPU, held until
+ * the process exits), hence the limit: n <= B200DDP_SAMPLER_STATIC_MAX_N, beyond
+ * which the call fails with B200DDP_ETOOBIG.  It calls no cudaMalloc, cudaFree
+ * or allocating library routine.  The first call on each device resolves the
+ * array's device address; make that call outside any stream capture.  All calls
+ * on a device share the array: keep them on one stream (or order the streams),
+ * because calls that overlap on the GPU race on it. */
+#define B200DDP_SAMPLER_STATIC_MAX_N 65536
+int b200ddp_sampler_shard_static(int64_t n, int world, int rank, uint64_t seed, uint64_t epoch,
+                                 int shuffle, int drop_last, int64_t *out_dev, b200ddp_stream stream);
+
 #ifdef __cplusplus
 }
 #endif
