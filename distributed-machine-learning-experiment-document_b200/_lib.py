@@ -99,7 +99,9 @@ def check(rc: int, what: str = "") -> None:
 
 
 def ptr_array(ptrs) -> ctypes.Array:
-    """Host array of device pointers."""
+    """Host array of device pointers (a ready-made ctypes array passes through)."""
+    if isinstance(ptrs, ctypes.Array):
+        return ptrs
     return (c_void_p * max(len(ptrs), 1))(*ptrs)
 
 

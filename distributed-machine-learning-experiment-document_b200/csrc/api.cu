@@ -409,10 +409,15 @@ int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype) {
     if (ctx->world == 1) return B200DDP_ALGO_ONESHOT;
     const size_t bytes = (size_t)nelem * dtype_size(dtype);
     if (!ctx->peers_ready) return ctx->nccl_comm ? (int)B200DDP_ALGO_NCCL : (int)B200DDP_ESTATE;
-    // one-shot moves (N-1) x S per GPU in one pass and wins while latency
-    // dominates; two-shot moves 2 (N-1)/N x S in two passes.
-    const size_t oneshot_max = (size_t)(ctx->world <= 2 ? 8 : ctx->world <= 4 ? 2 : 1) << 20;
-    return bytes <= oneshot_max ? B200DDP_ALGO_ONESHOT : B200DDP_ALGO_TWOSHOT;
+    // Crossovers measured on 2 and 8 B200s (profiles/r01_sweep_*.jsonl).  One-shot moves (N-1) x S
+    // per GPU and only pays off while the bucket is so small that saving the separate update
+    // launch (fused one-shot + SGD) matters; two-shot moves 2 (N-1)/N x S and beats NCCL up to
+    // ~128 MB (579 vs 419 GB/s busbw at 64 MB, 8 GPUs); above that NCCL's in-switch (NVLS)
+    // reduction wins (727 vs 646 GB/s at 1 GiB).
+    const size_t oneshot_max = (size_t)(ctx->world <= 2 ? 1024 : ctx->world <= 4 ? 512 : 256) << 10;
+    if (bytes <= oneshot_max) return B200DDP_ALGO_ONESHOT;
+    if (ctx->world > 4 && ctx->nccl_comm && bytes > ((size_t)128 << 20)) return B200DDP_ALGO_NCCL;
+    return B200DDP_ALGO_TWOSHOT;
 }
 
 int b200ddp_allreduce(b200ddp_ctx *ctx, size_t offset_bytes, int64_t nelem, int dtype, int algo,

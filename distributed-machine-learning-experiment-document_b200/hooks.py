@@ -9,16 +9,15 @@ codes/task2/dist_utils.py:39-42); this entry point exists because the north
 star names it.  Contract kept: the future resolves to a tensor shaped like
 bucket.buffer(); gradients arrive un-divided and leave averaged.
 """
-from __future__ import annotations
-
 import torch
+import torch.distributed as dist
 
 from . import _lib
 from .runtime import Context, default_context, dtype_code
 
 
 class HookState:
-    def __init__(self, ctx: Context | None = None, bucket_dtype="fp32", algo="auto"):
+    def __init__(self, ctx: "Context | None" = None, bucket_dtype="fp32", algo="auto"):
         self.ctx = ctx
         self.dtype = dtype_code(bucket_dtype)
         self.algo = algo
@@ -44,7 +43,8 @@ class HookState:
         return self._plans[key], self._offsets[key]
 
 
-def comm_hook(state: HookState, bucket) -> "torch.futures.Future[torch.Tensor]":
+def comm_hook(state: HookState, bucket: dist.GradBucket) -> torch.futures.Future[torch.Tensor]:
+    # DDP checks this exact return annotation (torch/nn/parallel/distributed.py:2280-2290)
     buf = bucket.buffer()
     if buf.dtype != torch.float32:
         raise _lib.B200DDPError("b200ddp.comm_hook expects fp32 gradient buckets")
