@@ -22,36 +22,14 @@ void set_error(const char *fmt, ...) {
 
 static size_t dtype_size(int dtype) { return dtype == B200DDP_BF16 ? 2 : 4; }
 
-PlanView plan_view(const b200ddp_plan *plan) {
-    PlanView pv;
-    pv.meta = plan->d_meta;
-    pv.chunks = plan->d_chunks;
-    pv.nchunks = (int)plan->chunks.size();
-    pv.T = plan->T;
-    for (int k = 0; k < kNumPtrKinds; ++k) pv.ptrs[k] = plan->d_ptrs + (size_t)k * plan->T;
-    return pv;
-}
-
-// Device pointer tables are refreshed only when a pointer changed (p.grad is
-// re-allocated by autograd every step; params and momentum never move).
-int plan_upload(b200ddp_plan *plan, PtrKind kind, const void *const *host_ptrs, cudaStream_t s) {
-    const int T = plan->T;
-    if (T == 0) return B200DDP_OK;
+// The caller's pointer arrays are read on the host at launch time and copied into the
+// kernel parameters; only their shape is checked here.
+int check_ptrs(const b200ddp_plan *plan, PtrKind kind, const void *const *host_ptrs) {
+    if (plan->T == 0) return B200DDP_OK;
     B2_REQUIRE(host_ptrs != nullptr, B200DDP_EINVAL, "pointer table %d is NULL", (int)kind);
-    for (int t = 0; t < T; ++t)
+    for (int t = 0; t < plan->T; ++t)
         B2_REQUIRE(host_ptrs[t] != nullptr || plan->meta[t].numel == 0, B200DDP_EINVAL,
                    "tensor %d of pointer table %d is NULL", t, (int)kind);
-    void **mirror = plan->h_ptrs.data() + (size_t)kind * T;
-    if (plan->uploaded[kind] && memcmp(mirror, host_ptrs, sizeof(void *) * T) == 0) return B200DDP_OK;
-    const int slot = plan->ring_pos;
-    plan->ring_pos = (slot + 1) % b200ddp_plan::kRing;
-    B2_CHECK_CUDA(cudaEventSynchronize(plan->pinned_ev[slot]));   // slot free again (no-op if never recorded)
-    memcpy(plan->pinned[slot], host_ptrs, sizeof(void *) * T);
-    B2_CHECK_CUDA(cudaMemcpyAsync(plan->d_ptrs + (size_t)kind * T, plan->pinned[slot], sizeof(void *) * T,
-                                  cudaMemcpyHostToDevice, s));
-    B2_CHECK_CUDA(cudaEventRecord(plan->pinned_ev[slot], s));
-    memcpy(mirror, host_ptrs, sizeof(void *) * T);
-    plan->uploaded[kind] = true;
     return B200DDP_OK;
 }
 
@@ -126,14 +104,17 @@ int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200dd
     const size_t flag_bytes = sizeof(uint32_t) * kMaxBlocksP2P * B200DDP_MAX_WORLD;
     cudaError_t e = cudaMalloc((void **)&ctx->staging, 2 * ctx->staging_bytes + 256);
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->flags, flag_bytes);
+    if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->block_gen, sizeof(uint32_t) * kMaxBlocksP2P);
     if (e == cudaSuccess) e = cudaMemset(ctx->staging, 0, 2 * ctx->staging_bytes + 256);
     if (e == cudaSuccess) e = cudaMemset(ctx->flags, 0, flag_bytes);
+    if (e == cudaSuccess) e = cudaMemset(ctx->block_gen, 0, sizeof(uint32_t) * kMaxBlocksP2P);
     if (e == cudaSuccess) e = cudaDeviceSynchronize();
     if (e != cudaSuccess) {
         set_error("allocating %zu bytes of staging on device %d failed: %s", 2 * ctx->staging_bytes, device,
                   cudaGetErrorString(e));
         cudaFree(ctx->staging);
         cudaFree(ctx->flags);
+        cudaFree(ctx->block_gen);
         delete ctx;
         return B200DDP_ECUDA;
     }
@@ -163,6 +144,7 @@ int b200ddp_destroy(b200ddp_ctx *ctx) {
     cudaFree(ctx->sampler_scratch);
     cudaFree(ctx->staging);
     cudaFree(ctx->flags);
+    cudaFree(ctx->block_gen);
     cudaGetLastError();
     delete ctx;
     return B200DDP_OK;
@@ -270,11 +252,18 @@ int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int buck
     p->T = T;
     p->dtype = bucket_dtype;
     int64_t off = 0;
+    Segment sg{0, 0, 0, 0};
     for (int t = 0; t < T; ++t) {
         if (numels[t] < 0) {
             set_error("tensor %d has negative numel", t);
             delete p;
             return B200DDP_EINVAL;
+        }
+        if (t - sg.t0 == kTabLarge) {            // table full: close the segment, open the next
+            sg.t1 = t;
+            sg.c1 = (int)p->chunks.size();
+            p->segments.push_back(sg);
+            sg = Segment{t, t, sg.c1, sg.c1};
         }
         p->meta.push_back({numels[t], off});
         const int64_t nch = (numels[t] + kChunk - 1) / kChunk;
@@ -283,25 +272,20 @@ int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int buck
             delete p;
             return B200DDP_ETOOBIG;
         }
-        for (int64_t c = 0; c < nch; ++c) p->chunks.push_back({t, (int)c});
+        for (int64_t c = 0; c < nch; ++c) p->chunks.push_back({t - sg.t0, (int)c});
         off += (numels[t] + kBucketAlign - 1) / kBucketAlign * kBucketAlign;
     }
+    if (T > 0) {
+        sg.t1 = T;
+        sg.c1 = (int)p->chunks.size();
+        p->segments.push_back(sg);
+    }
     p->bucket_elems = off;
-    p->h_ptrs.assign((size_t)kNumPtrKinds * (T > 0 ? T : 1), nullptr);
     cudaError_t e = cudaSuccess;
-    const size_t nT = T > 0 ? T : 1, nC = p->chunks.empty() ? 1 : p->chunks.size();
-    if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_meta, sizeof(TensorMeta) * nT);
-    if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_chunks, sizeof(Chunk) * nC);
-    if (e == cudaSuccess) e = cudaMalloc((void **)&p->d_ptrs, sizeof(void *) * kNumPtrKinds * nT);
-    if (e == cudaSuccess) e = cudaMemset(p->d_ptrs, 0, sizeof(void *) * kNumPtrKinds * nT);
-    if (e == cudaSuccess && T > 0)
-        e = cudaMemcpy(p->d_meta, p->meta.data(), sizeof(TensorMeta) * T, cudaMemcpyHostToDevice);
+    const size_t nC = p->chunks.empty() ? 1 : p->chunks.size();
+    e = cudaMalloc((void **)&p->d_chunks, sizeof(Chunk) * nC);
     if (e == cudaSuccess && !p->chunks.empty())
         e = cudaMemcpy(p->d_chunks, p->chunks.data(), sizeof(Chunk) * p->chunks.size(), cudaMemcpyHostToDevice);
-    for (int i = 0; i < b200ddp_plan::kRing && e == cudaSuccess; ++i) {
-        e = cudaMallocHost((void **)&p->pinned[i], sizeof(void *) * nT);
-        if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->pinned_ev[i], cudaEventDisableTiming);
-    }
     if (e != cudaSuccess) {
         set_error("plan allocation failed: %s", cudaGetErrorString(e));
         b200ddp_plan_destroy(p);
@@ -316,16 +300,7 @@ int b200ddp_plan_destroy(b200ddp_plan *p) {
     int prev = -1;
     cudaGetDevice(&prev);
     cudaSetDevice(p->device);
-    for (int i = 0; i < b200ddp_plan::kRing; ++i) {
-        if (p->pinned_ev[i]) {
-            cudaEventSynchronize(p->pinned_ev[i]);
-            cudaEventDestroy(p->pinned_ev[i]);
-        }
-        if (p->pinned[i]) cudaFreeHost(p->pinned[i]);
-    }
-    cudaFree(p->d_meta);
     cudaFree(p->d_chunks);
-    cudaFree(p->d_ptrs);
     if (prev >= 0) cudaSetDevice(prev);
     cudaGetLastError();   // teardown never leaves a stale error behind for the next launch check
     delete p;
@@ -348,8 +323,8 @@ int b200ddp_pack_scale(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *
     B2_REQUIRE(((uintptr_t)bucket & 15) == 0, B200DDP_EINVAL, "bucket must be 16-byte aligned");
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
-    if (int rc = plan_upload(plan, kGradIn, grads, s)) return rc;
-    return launch_pack(plan_view(plan), plan->dtype, bucket, scale, ctx->sm_count, s);
+    if (int rc = check_ptrs(plan, kGradIn, grads)) return rc;
+    return launch_pack(plan, grads, bucket, scale, ctx->sm_count, s);
 }
 
 int b200ddp_unpack(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, void *const *grads_out, float divisor,
@@ -360,17 +335,26 @@ int b200ddp_unpack(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, voi
     B2_REQUIRE(divisor != 0.0f && std::isfinite(divisor), B200DDP_EINVAL, "bad divisor");
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
-    if (int rc = plan_upload(plan, kGradOut, (const void *const *)grads_out, s)) return rc;
-    return launch_unpack(plan_view(plan), plan->dtype, bucket, divisor, ctx->sm_count, s);
+    if (int rc = check_ptrs(plan, kGradOut, (const void *const *)grads_out)) return rc;
+    return launch_unpack(plan, bucket, (const void *const *)grads_out, divisor, ctx->sm_count, s);
 }
 
-static int upload_update_tables(b200ddp_plan *plan, const SgdScalars &hp, void *const *params, void *const *moms,
-                                void *const *grads_out, cudaStream_t s) {
-    if (int rc = plan_upload(plan, kParam, (const void *const *)params, s)) return rc;
-    if (hp.has_momentum)
-        if (int rc = plan_upload(plan, kMom, (const void *const *)moms, s)) return rc;
-    if (grads_out)
-        if (int rc = plan_upload(plan, kGradOut, (const void *const *)grads_out, s)) return rc;
+static int update_tables(const b200ddp_plan *plan, const SgdScalars &hp, const void *const *grads,
+                         void *const *params, void *const *moms, void *const *grads_out, PtrArrays *pa) {
+    if (int rc = check_ptrs(plan, kParam, (const void *const *)params)) return rc;
+    pa->k[kParam] = (const void *const *)params;
+    if (grads) {
+        if (int rc = check_ptrs(plan, kGradIn, grads)) return rc;
+        pa->k[kGradIn] = grads;
+    }
+    if (hp.has_momentum) {
+        if (int rc = check_ptrs(plan, kMom, (const void *const *)moms)) return rc;
+        pa->k[kMom] = (const void *const *)moms;
+    }
+    if (grads_out) {
+        if (int rc = check_ptrs(plan, kGradOut, (const void *const *)grads_out)) return rc;
+        pa->k[kGradOut] = (const void *const *)grads_out;
+    }
     return B200DDP_OK;
 }
 
@@ -385,8 +369,9 @@ int b200ddp_unpack_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket,
     if (plan->bucket_elems == 0) return B200DDP_OK;
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
-    if (int rc = upload_update_tables(plan, hp, params, moms, grads_out, s)) return rc;
-    return launch_update(plan_view(plan), plan->dtype, bucket, grads_out != nullptr, hp, ctx->sm_count, s);
+    PtrArrays pa;
+    if (int rc = update_tables(plan, hp, nullptr, params, moms, grads_out, &pa)) return rc;
+    return launch_update(plan, bucket, pa, hp, ctx->sm_count, s);
 }
 
 int b200ddp_sgd_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads, void *const *params,
@@ -397,10 +382,11 @@ int b200ddp_sgd_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *gr
     if (plan->bucket_elems == 0) return B200DDP_OK;
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
-    if (int rc = plan_upload(plan, kGradIn, grads, s)) return rc;
-    if (int rc = upload_update_tables(plan, hp, params, moms, nullptr, s)) return rc;
-    // direct mode: bucket == nullptr makes the kernel read ptrs[kGradIn]
-    return launch_update(plan_view(plan), B200DDP_F32, nullptr, false, hp, ctx->sm_count, s);
+    B2_REQUIRE(grads != nullptr, B200DDP_EINVAL, "pointer table %d is NULL", (int)kGradIn);
+    PtrArrays pa;
+    if (int rc = update_tables(plan, hp, grads, params, moms, nullptr, &pa)) return rc;
+    // direct mode: bucket == nullptr makes the kernel read the gradient tensors themselves
+    return launch_update(plan, nullptr, pa, hp, ctx->sm_count, s);
 }
 
 // ------------------------------------------------------------------------ K2
@@ -453,11 +439,10 @@ int b200ddp_allreduce_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, size_t offset_by
     B2_REQUIRE(ctx->peers_ready, B200DDP_ESTATE, "peer memory not opened");
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
-    if (int rc = upload_update_tables(plan, hp, params, moms, grads_out, s)) return rc;
-    if (ctx->world == 1)
-        return launch_update(plan_view(plan), plan->dtype, ctx->staging + offset_bytes, grads_out != nullptr, hp,
-                             ctx->sm_count, s);
-    return launch_oneshot_update(ctx, plan_view(plan), plan->dtype, offset_bytes, grads_out != nullptr, hp, s);
+    PtrArrays pa;
+    if (int rc = update_tables(plan, hp, nullptr, params, moms, grads_out, &pa)) return rc;
+    if (ctx->world == 1) return launch_update(plan, ctx->staging + offset_bytes, pa, hp, ctx->sm_count, s);
+    return launch_oneshot_update(ctx, plan, offset_bytes, pa, hp, s);
 }
 
 // ----------------------------------------------------------------- emulation
@@ -469,8 +454,8 @@ static int check_emu(b200ddp_ctx *const *ctxs, int n) {
                    ctxs[r]->rank, ctxs[r]->world);
         B2_REQUIRE(ctxs[r]->device == ctxs[0]->device, B200DDP_EINVAL, "emulated ranks must share one device");
         B2_REQUIRE(ctxs[r]->peers_ready, B200DDP_ESTATE, "ctx %d has no peers", r);
-        B2_REQUIRE(ctxs[r]->staging_bytes == ctxs[0]->staging_bytes && ctxs[r]->epoch == ctxs[0]->epoch,
-                   B200DDP_ESTATE, "emulated contexts out of step");
+        B2_REQUIRE(ctxs[r]->staging_bytes == ctxs[0]->staging_bytes, B200DDP_ESTATE,
+                   "emulated contexts differ in staging size");
     }
     return B200DDP_OK;
 }
@@ -499,20 +484,19 @@ int b200ddp_emu_allreduce_sgd(b200ddp_ctx *const *ctxs, b200ddp_plan *const *pla
     B2_REQUIRE(!hp.has_momentum || moms != nullptr, B200DDP_EINVAL, "momentum buffers missing");
     cudaStream_t s = (cudaStream_t)stream;
     B2_CHECK_CUDA(cudaSetDevice(ctxs[0]->device));
-    PlanView pvs[B200DDP_MAX_WORLD];
+    PtrArrays pas[B200DDP_MAX_WORLD];
     for (int r = 0; r < n; ++r) {
         if (int rc = check_plan(ctxs[r], plans[r])) return rc;
         B2_REQUIRE(plans[r]->bucket_elems == plans[0]->bucket_elems && plans[r]->T == plans[0]->T &&
                        plans[r]->dtype == plans[0]->dtype,
                    B200DDP_EINVAL, "plans differ across emulated ranks");
-        if (int rc = upload_update_tables(plans[r], hp, params[r], moms ? moms[r] : nullptr,
-                                          grads_out ? grads_out[r] : nullptr, s))
+        if (int rc = update_tables(plans[r], hp, nullptr, params[r], moms ? moms[r] : nullptr,
+                                   grads_out ? grads_out[r] : nullptr, &pas[r]))
             return rc;
-        pvs[r] = plan_view(plans[r]);
     }
     if (int rc = in_staging(ctxs[0], offset_bytes, plans[0]->bucket_elems, plans[0]->dtype)) return rc;
     if (plans[0]->bucket_elems == 0) return B200DDP_OK;
-    return launch_oneshot_update_emu(ctxs, pvs, n, plans[0]->dtype, offset_bytes, grads_out != nullptr, hp, s);
+    return launch_oneshot_update_emu(ctxs, plans, n, offset_bytes, pas, hp, s);
 }
 
 // ------------------------------------------------------------------------ K4

@@ -37,25 +37,33 @@ constexpr int kChunk = kThreads * kVec * kUnroll;  // 2048 elements of one tenso
 constexpr int kBucketAlign = 32;       // tensor offsets in the bucket, in elements
 constexpr int kMaxBlocksP2P = 1024;    // flag slots: [block][src rank]
 constexpr int kSmCount = 148;
+constexpr int kTabSmall = 32;          // tensors per launch, small table (1.5 KB of kernel parameters)
+constexpr int kTabLarge = 256;         // tensors per launch, large table (12 KB); longer lists go in segments
 
 struct TensorMeta {       // immutable per plan
     int64_t numel;
     int64_t bucket_off;   // elements
 };
 struct Chunk {            // immutable per plan: one kChunk-sized piece of one tensor
-    int tensor;
+    int tensor;           // index inside the chunk's segment
     int index;            // chunk number inside the tensor
+};
+struct Segment {          // at most kTabLarge consecutive tensors = one kernel launch
+    int t0, t1;           // tensors [t0, t1)
+    int c0, c1;           // chunks [c0, c1) of the plan's chunk table
 };
 
 enum PtrKind { kGradIn = 0, kParam = 1, kMom = 2, kGradOut = 3, kNumPtrKinds = 4 };
 
-// Device view of a plan, passed to kernels by value.
-struct PlanView {
-    const TensorMeta *meta;
-    const Chunk *chunks;
-    int nchunks;
-    int T;
-    void *const *ptrs[kNumPtrKinds];   // each: T device pointers (device array)
+// Per-launch tensor table, passed BY VALUE as a __grid_constant__ kernel
+// parameter: sizes, bucket offsets and raw pointers sit in the constant bank.
+// No device-side pointer table has to be kept in step with torch's allocator
+// (p.grad moves every step), nothing is uploaded, and a launch captured in a
+// CUDA graph carries its pointers with it.
+template <int CAP, int NK> struct TensorTab {
+    long long numel[CAP];
+    long long boff[CAP];
+    void *ptr[NK][CAP];
 };
 
 struct SgdScalars {   // host-side casts follow torch: scalars are cast to fp32 once
@@ -74,11 +82,11 @@ struct b200ddp_ctx {
     int rank = 0, world = 1, device = 0;
     size_t staging_bytes = 0;          // one half
     char *staging = nullptr;           // 2 x staging_bytes
-    uint32_t *flags = nullptr;         // kMaxBlocksP2P x MAX_WORLD
+    uint32_t *flags = nullptr;         // peer-visible: kMaxBlocksP2P x MAX_WORLD
+    uint32_t *block_gen = nullptr;     // local: barrier generation of each block index, advanced by the kernels
     bool peers_ready = false;
     bool peers_ipc = false;
     b200ddp::PeerTable peers{};
-    uint32_t epoch = 0;                // barrier generation, identical on every rank
     void *nccl_comm = nullptr;
     int sm_count = b200ddp::kSmCount;
     // sampler scratch
@@ -95,30 +103,27 @@ struct b200ddp_plan {
     int64_t bucket_elems = 0;
     std::vector<b200ddp::TensorMeta> meta;
     std::vector<b200ddp::Chunk> chunks;
-    // device tables
-    b200ddp::TensorMeta *d_meta = nullptr;
-    b200ddp::Chunk *d_chunks = nullptr;
-    void **d_ptrs = nullptr;                    // kNumPtrKinds x T
-    // host mirrors + upload ring
-    std::vector<void *> h_ptrs;                 // last uploaded values, kNumPtrKinds x T
-    bool uploaded[b200ddp::kNumPtrKinds] = {false, false, false, false};
-    static constexpr int kRing = 8;
-    void **pinned[kRing] = {};
-    cudaEvent_t pinned_ev[kRing] = {};
-    int ring_pos = 0;
+    std::vector<b200ddp::Segment> segments;
+    b200ddp::Chunk *d_chunks = nullptr;   // the only device-side table: static, written once
 };
 
 namespace b200ddp {
 
+// Host view of one call: the plan plus the caller's pointer arrays (nullable per kind).
+struct PtrArrays {
+    const void *const *k[kNumPtrKinds] = {nullptr, nullptr, nullptr, nullptr};
+};
+
 // api.cu
-int plan_upload(b200ddp_plan *plan, PtrKind kind, const void *const *host_ptrs, cudaStream_t s);
-PlanView plan_view(const b200ddp_plan *plan);
 int sgd_scalars(const b200ddp_sgd_args *a, SgdScalars *out);
+int check_ptrs(const b200ddp_plan *plan, PtrKind kind, const void *const *host_ptrs);
 
 // pack_update.cu
-int launch_pack(const PlanView &pv, int dtype, void *bucket, float scale, int sm_count, cudaStream_t s);
-int launch_unpack(const PlanView &pv, int dtype, const void *bucket, float divisor, int sm_count, cudaStream_t s);
-int launch_update(const PlanView &pv, int dtype, const void *bucket /*null: direct*/, bool write_grad,
+int launch_pack(const b200ddp_plan *plan, const void *const *grads, void *bucket, float scale, int sm_count,
+                cudaStream_t s);
+int launch_unpack(const b200ddp_plan *plan, const void *bucket, const void *const *grads_out, float divisor,
+                  int sm_count, cudaStream_t s);
+int launch_update(const b200ddp_plan *plan, const void *bucket /*null: direct*/, const PtrArrays &pa,
                   const SgdScalars &hp, int sm_count, cudaStream_t s);
 
 // p2p.cu
@@ -126,10 +131,10 @@ int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int sm_count);
 int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, int algo, cudaStream_t s);
 int launch_p2p_allreduce_emu(b200ddp_ctx *const *ctxs, int n, size_t off, int64_t nelem, int dtype,
                              int algo, cudaStream_t s);
-int launch_oneshot_update(b200ddp_ctx *ctx, const PlanView &pv, int dtype, size_t off, bool write_grad,
+int launch_oneshot_update(b200ddp_ctx *ctx, const b200ddp_plan *plan, size_t off, const PtrArrays &pa,
                           const SgdScalars &hp, cudaStream_t s);
-int launch_oneshot_update_emu(b200ddp_ctx *const *ctxs, const PlanView *pvs, int n, int dtype, size_t off,
-                              bool write_grad, const SgdScalars &hp, cudaStream_t s);
+int launch_oneshot_update_emu(b200ddp_ctx *const *ctxs, b200ddp_plan *const *plans, int n, size_t off,
+                              const PtrArrays *pas, const SgdScalars &hp, cudaStream_t s);
 
 // nccl_dyn.cpp
 int nccl_unique_id(void *out128);

@@ -109,7 +109,10 @@ struct P2PArgs {
     size_t off_bytes;       // bucket inside the first staging half
     size_t result_off;      // one-shot: where the sums go (own staging)
     int64_t nvec;           // 16-byte vectors in the bucket
-    uint32_t gen;           // barrier generations gen+1, gen+2
+    // Barrier generation of block b of rank r lives in gen[r][b] (device memory, local to rank r)
+    // and is advanced by the kernel itself: a launch replayed from a CUDA graph must not carry
+    // a generation number frozen at capture time.  EMU fills all ranks, a real launch only its own.
+    uint32_t *gen[B200DDP_MAX_WORLD];
 };
 
 // N > 0: unrolled for that world size; N == 0: runtime loop over args.world.
@@ -118,7 +121,8 @@ __global__ void __launch_bounds__(kP2PThreads) oneshot_kernel(P2PArgs a) {
     const int rank = EMU ? (int)blockIdx.y : a.rank;
     const int world = N > 0 ? N : a.world;
     const int bid = blockIdx.x;
-    peer_barrier(a.pt, rank, world, bid, a.gen + 1);
+    const uint32_t gen = a.gen[rank][bid];
+    peer_barrier(a.pt, rank, world, bid, gen + 1);
     uint4 *dst = reinterpret_cast<uint4 *>(a.pt.staging[rank] + a.result_off);
     const int64_t stride = (int64_t)gridDim.x * kP2PThreads;
     for (int64_t i = (int64_t)bid * kP2PThreads + threadIdx.x; i < a.nvec; i += stride) {
@@ -137,7 +141,8 @@ __global__ void __launch_bounds__(kP2PThreads) oneshot_kernel(P2PArgs a) {
         }
         dst[i] = Vec16<BT>::pack(acc);
     }
-    peer_barrier(a.pt, rank, world, bid, a.gen + 2);
+    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
 template <typename BT, int N, bool EMU>
@@ -145,7 +150,8 @@ __global__ void __launch_bounds__(kP2PThreads) twoshot_kernel(P2PArgs a) {
     const int rank = EMU ? (int)blockIdx.y : a.rank;
     const int world = N > 0 ? N : a.world;
     const int bid = blockIdx.x;
-    peer_barrier(a.pt, rank, world, bid, a.gen + 1);
+    const uint32_t gen = a.gen[rank][bid];
+    peer_barrier(a.pt, rank, world, bid, gen + 1);
     const int64_t per = (a.nvec + world - 1) / world;
     const int64_t lo = per * rank;
     const int64_t hi = lo + per < a.nvec ? lo + per : a.nvec;
@@ -172,31 +178,39 @@ __global__ void __launch_bounds__(kP2PThreads) twoshot_kernel(P2PArgs a) {
             for (int r = 0; r < world; ++r) st_peer_u4(reinterpret_cast<uint4 *>(a.pt.staging[r] + a.off_bytes) + i, out);
         }
     }
-    peer_barrier(a.pt, rank, world, bid, a.gen + 2);
+    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
 // ---- fused one-shot reduce + update --------------------------------------------
-template <bool EMU> struct PlanSet { PlanView v[EMU ? B200DDP_MAX_WORLD : 1]; };
+// Tensor tables come by value in the kernel parameters (see TensorTab); under EMU every
+// emulated rank has its own table and its own chunk list.
+template <bool EMU, int CAP> struct TabSet {
+    TensorTab<CAP, kNumPtrKinds> t[EMU ? B200DDP_MAX_WORLD : 1];
+    const Chunk *chunks[EMU ? B200DDP_MAX_WORLD : 1];
+};
 
-template <typename BT, bool WRITE_GRAD, bool EMU>
-__global__ void __launch_bounds__(kThreads) oneshot_update_kernel(P2PArgs a, PlanSet<EMU> ps, SgdScalars hp) {
+template <typename BT, bool WRITE_GRAD, bool EMU, int CAP>
+__global__ void __launch_bounds__(kThreads) oneshot_update_kernel(P2PArgs a, const __grid_constant__ TabSet<EMU, CAP> ts,
+                                                                  int nchunks, SgdScalars hp) {
     const int rank = EMU ? (int)blockIdx.y : a.rank;
     const int world = a.world;
     const int bid = blockIdx.x;
-    const PlanView &pv = ps.v[EMU ? rank : 0];
+    const TensorTab<CAP, kNumPtrKinds> &tab = ts.t[EMU ? rank : 0];
+    const Chunk *chunks = ts.chunks[EMU ? rank : 0];
     const int tid = threadIdx.x;
     const bool load_m = hp.has_momentum && !hp.first_step;
-    peer_barrier(a.pt, rank, world, bid, a.gen + 1);
-    for (int c = bid; c < pv.nchunks; c += gridDim.x) {
-        const Chunk ck = pv.chunks[c];
-        const TensorMeta tm = pv.meta[ck.tensor];
+    const uint32_t gen = a.gen[rank][bid];
+    peer_barrier(a.pt, rank, world, bid, gen + 1);
+    for (int c = bid; c < nchunks; c += gridDim.x) {
+        const Chunk ck = chunks[c];
         const int64_t e0 = (int64_t)ck.index * kChunk;
-        const int64_t left = tm.numel - e0;
+        const int64_t left = tab.numel[ck.tensor] - e0;
         const int count = left < kChunk ? (int)left : kChunk;
-        const int64_t boff = tm.bucket_off + e0;
-        float *p = (float *)pv.ptrs[kParam][ck.tensor] + e0;
-        float *m = hp.has_momentum ? (float *)pv.ptrs[kMom][ck.tensor] + e0 : nullptr;
-        float *go = WRITE_GRAD ? (float *)pv.ptrs[kGradOut][ck.tensor] + e0 : nullptr;
+        const int64_t boff = tab.boff[ck.tensor] + e0;
+        float *p = (float *)tab.ptr[kParam][ck.tensor] + e0;
+        float *m = hp.has_momentum ? (float *)tab.ptr[kMom][ck.tensor] + e0 : nullptr;
+        float *go = WRITE_GRAD ? (float *)tab.ptr[kGradOut][ck.tensor] + e0 : nullptr;
         const bool aligned = (((uintptr_t)p | (uintptr_t)m | (uintptr_t)go) & 15) == 0;   // bucket side is aligned by layout
         const int nvec = aligned ? count / kVec : 0;
         for (int i = tid; i < nvec; i += kThreads) {
@@ -236,7 +250,8 @@ __global__ void __launch_bounds__(kThreads) oneshot_update_kernel(P2PArgs a, Pla
             if (WRITE_GRAD) go[i] = ga;
         }
     }
-    peer_barrier(a.pt, rank, world, bid, a.gen + 2);
+    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
 #define B2_LAUNCH_CHECK()                                                                              \
@@ -271,8 +286,36 @@ P2PArgs make_args(const b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype) 
     a.off_bytes = off;
     a.result_off = ctx->staging_bytes + off;
     a.nvec = nelem * (dtype == B200DDP_BF16 ? 2 : 4) / 16;
-    a.gen = ctx->epoch;
+    for (int r = 0; r < B200DDP_MAX_WORLD; ++r) a.gen[r] = nullptr;
+    a.gen[ctx->rank] = ctx->block_gen;
     return a;
+}
+
+template <int CAP>
+void fill_update_tab(TensorTab<CAP, kNumPtrKinds> &tab, const b200ddp_plan *plan, const Segment &sg, const PtrArrays &pa) {
+    const int n = sg.t1 - sg.t0;
+    for (int i = 0; i < n; ++i) {
+        tab.numel[i] = plan->meta[sg.t0 + i].numel;
+        tab.boff[i] = plan->meta[sg.t0 + i].bucket_off;
+    }
+    for (int k = 0; k < kNumPtrKinds; ++k)
+        for (int i = 0; i < n; ++i) tab.ptr[k][i] = pa.k[k] ? const_cast<void *>(pa.k[k][sg.t0 + i]) : nullptr;
+}
+
+int update_grid(int nchunks) { return nchunks < 2 * kSmCount ? nchunks : 2 * kSmCount; }
+
+template <typename BT, bool WG, int CAP>
+int run_fused(b200ddp_ctx *ctx, const b200ddp_plan *plan, const Segment &sg, size_t off, const PtrArrays &pa,
+              const SgdScalars &hp, cudaStream_t s) {
+    P2PArgs a = make_args(ctx, off, 0, plan->dtype);
+    TabSet<false, CAP> ts;
+    fill_update_tab(ts.t[0], plan, sg, pa);
+    ts.chunks[0] = plan->d_chunks + sg.c0;
+    const int n = sg.c1 - sg.c0;
+    cudaGetLastError();
+    oneshot_update_kernel<BT, WG, false, CAP><<<update_grid(n), kThreads, 0, s>>>(a, ts, n, hp);
+    B2_LAUNCH_CHECK();
+    return B200DDP_OK;
 }
 
 }  // namespace
@@ -295,13 +338,13 @@ int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype,
     const void *k = pick<false>(dtype, algo, ctx->world);
     void *params[] = {&a};
     B2_CHECK_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kP2PThreads), params, 0, s));
-    ctx->epoch += 2;
     return B200DDP_OK;
 }
 
 int launch_p2p_allreduce_emu(b200ddp_ctx *const *ctxs, int n, size_t off, int64_t nelem, int dtype, int algo,
                              cudaStream_t s) {
     P2PArgs a = make_args(ctxs[0], off, nelem, dtype);
+    for (int r = 0; r < n; ++r) a.gen[r] = ctxs[r]->block_gen;
     const void *k = pick<true>(dtype, algo, n);
     int per_sm = 0;
     B2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kP2PThreads, 0));
@@ -311,53 +354,58 @@ int launch_p2p_allreduce_emu(b200ddp_ctx *const *ctxs, int n, size_t off, int64_
     if (grid > fit) grid = fit;
     void *params[] = {&a};
     B2_CHECK_CUDA(cudaLaunchCooperativeKernel(k, dim3(grid, n), dim3(kP2PThreads), params, 0, s));
-    for (int r = 0; r < n; ++r) ctxs[r]->epoch += 2;
     return B200DDP_OK;
 }
 
-static int update_grid(int nchunks) { return nchunks < 2 * kSmCount ? nchunks : 2 * kSmCount; }
-
-int launch_oneshot_update(b200ddp_ctx *ctx, const PlanView &pv, int dtype, size_t off, bool write_grad,
+int launch_oneshot_update(b200ddp_ctx *ctx, const b200ddp_plan *plan, size_t off, const PtrArrays &pa,
                           const SgdScalars &hp, cudaStream_t s) {
-    P2PArgs a = make_args(ctx, off, 0, dtype);
-    PlanSet<false> ps;
-    ps.v[0] = pv;
-    const int grid = update_grid(pv.nchunks);
-    cudaGetLastError();
-#define B2_FUSED(BT, WG) oneshot_update_kernel<BT, WG, false><<<grid, kThreads, 0, s>>>(a, ps, hp)
-    if (dtype == B200DDP_F32) {
-        if (write_grad) B2_FUSED(float, true); else B2_FUSED(float, false);
-    } else {
-        if (write_grad) B2_FUSED(__nv_bfloat16, true); else B2_FUSED(__nv_bfloat16, false);
-    }
+    const bool wg = pa.k[kGradOut] != nullptr;
+    for (const Segment &sg : plan->segments) {
+        if (sg.c1 == sg.c0) continue;
+        const bool small = sg.t1 - sg.t0 <= kTabSmall;
+        int rc;
+#define B2_FUSED(BT, WG) (small ? run_fused<BT, WG, kTabSmall>(ctx, plan, sg, off, pa, hp, s) \
+                                : run_fused<BT, WG, kTabLarge>(ctx, plan, sg, off, pa, hp, s))
+        if (plan->dtype == B200DDP_F32) rc = wg ? B2_FUSED(float, true) : B2_FUSED(float, false);
+        else rc = wg ? B2_FUSED(__nv_bfloat16, true) : B2_FUSED(__nv_bfloat16, false);
 #undef B2_FUSED
-    B2_LAUNCH_CHECK();
-    ctx->epoch += 2;
+        if (rc) return rc;
+    }
     return B200DDP_OK;
 }
 
-int launch_oneshot_update_emu(b200ddp_ctx *const *ctxs, const PlanView *pvs, int n, int dtype, size_t off,
-                              bool write_grad, const SgdScalars &hp, cudaStream_t s) {
-    P2PArgs a = make_args(ctxs[0], off, 0, dtype);
-    PlanSet<true> ps;
-    for (int r = 0; r < n; ++r) ps.v[r] = pvs[r];
-    for (int r = n; r < B200DDP_MAX_WORLD; ++r) ps.v[r] = pvs[0];
+int launch_oneshot_update_emu(b200ddp_ctx *const *ctxs, b200ddp_plan *const *plans, int n, size_t off,
+                              const PtrArrays *pas, const SgdScalars &hp, cudaStream_t s) {
+    B2_REQUIRE(plans[0]->segments.size() <= 1 && plans[0]->T <= kTabSmall, B200DDP_ETOOBIG,
+               "the emulated fused kernel takes at most %d tensors", kTabSmall);
+    if (plans[0]->segments.empty() || plans[0]->chunks.empty()) return B200DDP_OK;
+    const Segment &sg = plans[0]->segments[0];
+    P2PArgs a = make_args(ctxs[0], off, 0, plans[0]->dtype);
+    static TabSet<true, kTabSmall> ts;   // 12 KB: keep it off the stack
+    for (int r = 0; r < B200DDP_MAX_WORLD; ++r) {
+        const int q = r < n ? r : 0;
+        a.gen[r] = ctxs[q]->block_gen;
+        fill_update_tab(ts.t[r], plans[q], plans[q]->segments[0], pas[q]);
+        ts.chunks[r] = plans[q]->d_chunks;
+    }
+    const bool wg = pas[0].k[kGradOut] != nullptr;
     const void *k;
-    if (dtype == B200DDP_F32)
-        k = write_grad ? (const void *)oneshot_update_kernel<float, true, true> : (const void *)oneshot_update_kernel<float, false, true>;
+    if (plans[0]->dtype == B200DDP_F32)
+        k = wg ? (const void *)oneshot_update_kernel<float, true, true, kTabSmall>
+               : (const void *)oneshot_update_kernel<float, false, true, kTabSmall>;
     else
-        k = write_grad ? (const void *)oneshot_update_kernel<__nv_bfloat16, true, true>
-                       : (const void *)oneshot_update_kernel<__nv_bfloat16, false, true>;
+        k = wg ? (const void *)oneshot_update_kernel<__nv_bfloat16, true, true, kTabSmall>
+               : (const void *)oneshot_update_kernel<__nv_bfloat16, false, true, kTabSmall>;
     int per_sm = 0;
     B2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kThreads, 0));
-    int grid = update_grid(pvs[0].nchunks);
+    int nchunks = sg.c1 - sg.c0;
+    int grid = update_grid(nchunks);
     const int fit = per_sm * ctxs[0]->sm_count / n;
     B2_REQUIRE(fit >= 1, B200DDP_ESTATE, "device cannot co-schedule %d emulated ranks", n);
     if (grid > fit) grid = fit;
     SgdScalars h = hp;
-    void *params[] = {&a, &ps, &h};
+    void *params[] = {&a, &ts, &nchunks, &h};
     B2_CHECK_CUDA(cudaLaunchCooperativeKernel(k, dim3(grid, n), dim3(kThreads), params, 0, s));
-    for (int r = 0; r < n; ++r) ctxs[r]->epoch += 2;
     return B200DDP_OK;
 }
 
