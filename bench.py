@@ -51,6 +51,8 @@ def parse():
     ap.add_argument("--algo", default="auto", choices=["auto", "nccl", "oneshot", "twoshot"])
     ap.add_argument("--mode", default="fused", choices=["fused", "strict"],
                     help="fused: sync folded into optimizer.step(); strict: p.grad averaged first")
+    ap.add_argument("--step", default="graph", choices=["graph", "eager"],
+                    help="graph: the loop body replayed from a CUDA graph; eager: the reference's Python loop")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--exact-warmup", action="store_true", help="do exactly --warmup steps (profiler runs)")
     ap.add_argument("--no-kernel-bench", action="store_true", help="skip the per-kernel roofline measurement")
@@ -438,12 +440,23 @@ def gpu_arm(args):
     h2d = host_batches[0][0].numel() * 4 + host_batches[0][1].numel() * 8
     k3 = []                      # (start, end) events around our sync+update kernels, per timed step
 
-    def step(i, e2e, record=False):
+    def total_launches():
+        return opt.launches + (b200ddp.dist_utils.engine_for(model).launches if args.mode == "strict" else 0)
+
+    gstep = b200ddp.GraphedTrainStep(model, loss_fn, opt) if args.step == "graph" else None
+    graph_info = {"launches_per_step": None}
+
+    def step(i, e2e, record=False, eager=False):
+        x, y = host_batches[i % 8] if e2e else dev_batches[i % 8]
+        if gstep is not None and not eager:
+            # public API: one call = forward, backward, sync, optimizer step (replayed from a CUDA graph)
+            before = total_launches()
+            loss = gstep(x, y)
+            if gstep.graph is not None and graph_info["launches_per_step"] is None:
+                graph_info["launches_per_step"] = total_launches() - before    # counted while capturing
+            return loss.item() if e2e else loss
         if e2e:
-            x, y = host_batches[i % 8]
             x, y = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
-        else:
-            x, y = dev_batches[i % 8]
         loss = loss_fn(model(x), y)
         opt.zero_grad()
         loss.backward()
@@ -462,12 +475,12 @@ def gpu_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    def timed(e2e, steps, record=False):
+    def timed(e2e, steps, record=False, eager=False):
         fence()
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record()
         for i in range(steps):
-            step(i, e2e, record)
+            step(i, e2e, record, eager)
         b.record()
         fence()
         t = torch.tensor([a.elapsed_time(b) * 1e-3], device=dev, dtype=torch.float64)
@@ -480,16 +493,21 @@ def gpu_arm(args):
     for i in range(warm):
         step(i, False)
     fence()
-    eng = b200ddp.dist_utils.engine_for(model)
-    launches0 = opt.launches + (eng.launches if args.mode == "strict" else 0)
+    graphed = gstep is not None and gstep.graph is not None
+    launches0 = total_launches()
     clocks = ClockSampler(local) if rank == 0 else None
-    t_dev = timed(False, args.steps, record=True)
-    launches = opt.launches + (eng.launches if args.mode == "strict" else 0) - launches0
+    t_dev = timed(False, args.steps, record=not graphed)
+    launches = graph_info["launches_per_step"] * args.steps if graphed else total_launches() - launches0
     for i in range(3):
         step(i, True)
     t_e2e = timed(True, args.steps)
     clk = clocks.stop() if clocks else None
-    ours_s = statistics.mean(a.elapsed_time(b) for a, b in k3) * 1e-3
+    t_eager = None
+    if graphed:                      # the same loop without the graph, for the record
+        for i in range(10):
+            step(i, False, eager=True)
+        t_eager = timed(False, args.steps, record=True, eager=True)
+    ours_s = statistics.mean(a.elapsed_time(b) for a, b in k3) * 1e-3 if k3 else None
 
     # ---- the dominant kernel of ours, against the measured HBM peak
     peaks = {}
@@ -525,7 +543,7 @@ def gpu_arm(args):
                     "launch_us": kern["us"],
                     "how": "CUDA events around 12 back-to-back launches rotating over 3 disjoint operand sets "
                            "(each launch reads data colder than L2), median of 5 rounds",
-                    "in_step_sync_plus_update_us": ours_s * 1e6}
+                    "in_step_sync_plus_update_us": ours_s * 1e6 if ours_s else None}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -540,7 +558,10 @@ def gpu_arm(args):
             "e2e": {"value": world * batch * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "ms_per_step": t_e2e / args.steps * 1e3},
             "gpu_launches": launches, "clocks": clk, "roofline": roofline,
-            "sync_update_ms_per_step": ours_s * 1e3}
+            "step_mode": ("cuda-graph replay of the loop body (b200ddp.GraphedTrainStep)" if graphed else
+                          "eager loop" + (f" (graph capture failed: {gstep.capture_error})" if gstep is not None else "")),
+            "eager_ms_per_step": t_eager / args.steps * 1e3 if t_eager else None,
+            "sync_update_ms_per_step_eager": ours_s * 1e3 if ours_s else None}
     line.update(extras)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_sample(1, name, batch, lr, args.cpu_budget_s)

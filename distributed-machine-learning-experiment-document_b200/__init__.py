@@ -15,12 +15,13 @@ from ._lib import B200DDPError
 from .dist_utils import (allgather_average_gradients, allreduce_average_gradients, average_gradients, configure,
                          dist_init, enable_fused_step, get_local_rank, get_world_size, init_parameters)
 from .engine import GradSync
+from .graph import GraphedTrainStep
 from .hooks import HookState, comm_hook
 from .optim import SGD
 from .runtime import Context, Plan, default_context, reset_default_context, sampler_sizes, sgd_args
 from .sampler import DistributedSampler, MySampler
 
-__all__ = ["B200DDPError", "Context", "Plan", "GradSync", "SGD", "DistributedSampler", "MySampler", "HookState",
+__all__ = ["B200DDPError", "Context", "Plan", "GradSync", "GraphedTrainStep", "SGD", "DistributedSampler", "MySampler", "HookState",
            "comm_hook", "dist_utils", "dist_init", "get_local_rank", "get_world_size", "init_parameters",
            "allreduce_average_gradients", "average_gradients", "allgather_average_gradients", "enable_fused_step",
            "configure", "default_context", "reset_default_context", "sampler_sizes", "sgd_args"]

@@ -136,3 +136,46 @@ def test_comm_hook_on_one_rank(default_ctx):
     fut = b200ddp.comm_hook(b200ddp.HookState(default_ctx), FakeBucket(g))
     out = fut.wait()
     assert out.data_ptr() == g.data_ptr() and torch.equal(out, want)
+
+
+def _mlp():
+    torch.manual_seed(3)
+    return torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 300), torch.nn.ReLU(),
+                               torch.nn.Linear(300, 100), torch.nn.ReLU(), torch.nn.Linear(100, 10)).cuda()
+
+
+@pytest.mark.parametrize("fused", [False, True])
+def test_graphed_train_step_equals_eager_loop(default_ctx, fused):
+    """b200ddp.GraphedTrainStep replays the reference's loop body from a CUDA graph;
+    it must leave exactly the state the eager loop leaves (linear layers only, so
+    forward/backward are run-to-run deterministic and the comparison is bit-exact)."""
+    results = []
+    for graphed in (False, True):
+        model = _mlp()
+        opt = b200ddp.SGD(model.parameters(), lr=0.01, momentum=0.9)
+        if fused:
+            b200ddp.enable_fused_step(model, opt)
+        loss_fn = torch.nn.CrossEntropyLoss()
+        step = b200ddp.GraphedTrainStep(model, loss_fn, opt, eager_steps=2) if graphed else None
+        losses = []
+        for s in range(9):
+            x, y = ref_ddp.synthetic_batch(0, s, 32, (1, 28, 28), 10)
+            if graphed:
+                losses.append(float(step(x.pin_memory(), y.pin_memory()).item()))
+            else:
+                x, y = x.cuda(), y.cuda()
+                loss = loss_fn(model(x), y)
+                opt.zero_grad()
+                loss.backward()
+                b200ddp.allreduce_average_gradients(model)
+                opt.step()
+                losses.append(float(loss.item()))
+        if graphed:
+            assert step.capture_error is None and step.graph is not None and step.calls == 9
+        results.append((losses, [p.detach().clone() for p in model.parameters()],
+                        [opt.state[p]["momentum_buffer"].clone() for p in model.parameters()],
+                        [p.grad.clone() for p in model.parameters()]))
+    (l0, p0, m0, g0), (l1, p1, m1, g1) = results
+    assert l0 == l1
+    for a, b in zip(p0 + m0 + g0, p1 + m1 + g1):
+        assert torch.equal(a, b)

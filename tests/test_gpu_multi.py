@@ -197,7 +197,54 @@ def _ddp_hook(rank, ws):
                 assert (a.grad - w).abs().max() <= 1e-5 * w.abs().max()
 
 
+def _graph_step(rank, ws, algo):
+    """GraphedTrainStep across ranks: the captured step contains the P2P kernels, whose
+    barrier generations live on the device - replays must stay in step with each other
+    and reproduce the eager loop bit for bit."""
+    import b200ddp
+    from oracle import ref_ddp
+    b200ddp.configure(algo=algo)
+    outs = []
+    for graphed in (False, True):
+        torch.manual_seed(5)
+        model = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 300), torch.nn.ReLU(),
+                                    torch.nn.Linear(300, 10)).cuda()
+        b200ddp.init_parameters(model)
+        opt = b200ddp.SGD(model.parameters(), lr=0.01, momentum=0.9)
+        b200ddp.enable_fused_step(model, opt)
+        loss_fn = torch.nn.CrossEntropyLoss()
+        step = b200ddp.GraphedTrainStep(model, loss_fn, opt, eager_steps=2) if graphed else None
+        for s in range(8):
+            x, y = ref_ddp.synthetic_batch(rank, s, 32, (1, 28, 28), 10)
+            x, y = x.cuda(), y.cuda()
+            if graphed:
+                step(x, y)
+            else:
+                loss = loss_fn(model(x), y)
+                opt.zero_grad()
+                loss.backward()
+                b200ddp.allreduce_average_gradients(model)
+                opt.step()
+        torch.cuda.synchronize()
+        if graphed:
+            assert step.capture_error is None and step.graph is not None, step.capture_error
+        outs.append(torch.cat([p.detach().flatten() for p in model.parameters()]))
+    assert torch.equal(outs[0], outs[1]), "graph replay diverged from the eager loop"
+    mine = outs[1].clone()
+    torch.distributed.broadcast(mine, 0)
+    assert torch.equal(mine, outs[1]), "ranks diverged"
+
+
 # ------------------------------------------------------------------ tests
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nccl"])
+def test_graphed_step_two_ranks(algo):
+    _run(2, _graph_step, algo)
+
+
+def test_graphed_step_eight_ranks():
+    _run(8, _graph_step, "auto")
+
+
 @pytest.mark.parametrize("algo,mode,dtype", [("nccl", "strict", "fp32"), ("oneshot", "strict", "fp32"),
                                              ("twoshot", "strict", "fp32"), ("oneshot", "fused", "fp32"),
                                              ("twoshot", "fused", "fp32"), ("auto", "fused", "bf16")])
