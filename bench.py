@@ -517,6 +517,32 @@ def gpu_arm(args):
         pass
     peak_gbs, peak_src = (peaks["hbm_gbs"], "measured") if "hbm_gbs" in peaks else (6650.0, "fallback")
     extras = {}
+    if world > 1:
+        # grad-sync bus bandwidth on this model's own bucket(s): 20 reductions back to back,
+        # max over ranks, busbw = S / t * 2 (N - 1) / N (nccl-tests convention)
+        eng = b200ddp.dist_utils.engine_for(model)
+        S = sum(bk.plan.bucket_bytes for bk in eng.buckets)
+        names = {v: k for k, v in b200ddp._lib.ALGO_NAMES.items()}
+        picked = sorted({names[eng.ctx.allreduce_pick(bk.plan.bucket_elems, eng.dtype)] if args.algo == "auto"
+                         else args.algo for bk in eng.buckets})
+        for _ in range(3):
+            for bk in eng.buckets:
+                eng.ctx.allreduce(bk.offset, bk.plan.bucket_elems, eng.dtype, args.algo)
+        fence()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(20):
+            for bk in eng.buckets:
+                eng.ctx.allreduce(bk.offset, bk.plan.bucket_elems, eng.dtype, args.algo)
+        b.record()
+        fence()
+        t = torch.tensor([a.elapsed_time(b) * 1e-3 / 20], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        t = float(t.item())
+        extras["grad_sync"] = {"bucket_bytes": S, "buckets": len(eng.buckets), "algo": picked, "us": t * 1e6,
+                               "algbw_gbs": S / t / 1e9, "busbw_gbs": S / t / 1e9 * 2 * (world - 1) / world,
+                               "nvlink_peak_gbs_per_direction": 900.0,
+                               "frac_of_nominal_nvlink": S / t / 1e9 * 2 * (world - 1) / world / 900.0}
     if rank == 0:
         ctx = b200ddp.default_context()
         if not args.no_kernel_bench:

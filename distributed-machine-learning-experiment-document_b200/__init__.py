@@ -12,7 +12,7 @@ identifier; the repo root carries a two-line alias package).
 """
 from . import _lib, dist_utils
 from ._lib import B200DDPError
-from .dist_utils import (allgather_average_gradients, allreduce_average_gradients, average_gradients, configure,
+from .dist_utils import (CommTimer, allgather_average_gradients, broadcast_from_rank0, allreduce_average_gradients, average_gradients, configure,
                          dist_init, enable_fused_step, get_local_rank, get_world_size, init_parameters)
 from .engine import GradSync
 from .graph import GraphedTrainStep
@@ -24,4 +24,4 @@ from .sampler import DistributedSampler, MySampler
 __all__ = ["B200DDPError", "Context", "Plan", "GradSync", "GraphedTrainStep", "SGD", "DistributedSampler", "MySampler", "HookState",
            "comm_hook", "dist_utils", "dist_init", "get_local_rank", "get_world_size", "init_parameters",
            "allreduce_average_gradients", "average_gradients", "allgather_average_gradients", "enable_fused_step",
-           "configure", "default_context", "reset_default_context", "sampler_sizes", "sgd_args"]
+           "configure", "CommTimer", "broadcast_from_rank0", "default_context", "reset_default_context", "sampler_sizes", "sgd_args"]

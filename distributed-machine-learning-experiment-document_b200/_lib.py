@@ -41,6 +41,7 @@ _SIGNATURES = {
     "b200ddp_destroy": (c_int, [c_void_p]),
     "b200ddp_staging": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]),
     "b200ddp_flags": (c_int, [c_void_p, POINTER(c_void_p)]),
+    "b200ddp_peer_staging": (c_int, [c_void_p, c_int, POINTER(c_void_p)]),
     "b200ddp_nccl_unique_id": (c_int, [c_void_p]),
     "b200ddp_nccl_init": (c_int, [c_void_p, c_void_p]),
     "b200ddp_ipc_export": (c_int, [c_void_p, c_void_p]),

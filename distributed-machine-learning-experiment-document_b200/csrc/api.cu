@@ -163,6 +163,14 @@ int b200ddp_flags(b200ddp_ctx *ctx, void **ptr) {
     return B200DDP_OK;
 }
 
+int b200ddp_peer_staging(b200ddp_ctx *ctx, int peer, void **ptr) {
+    B2_REQUIRE(ctx != nullptr && ptr != nullptr, B200DDP_EINVAL, "NULL argument");
+    B2_REQUIRE(peer >= 0 && peer < ctx->world, B200DDP_EINVAL, "peer %d not in [0, %d)", peer, ctx->world);
+    B2_REQUIRE(ctx->peers_ready && ctx->peers.staging[peer] != nullptr, B200DDP_ESTATE, "peer memory not opened");
+    *ptr = ctx->peers.staging[peer];
+    return B200DDP_OK;
+}
+
 int b200ddp_nccl_unique_id(void *out_uid) {
     B2_REQUIRE(out_uid != nullptr, B200DDP_EINVAL, "out is NULL");
     return nccl_unique_id(out_uid);

@@ -18,6 +18,7 @@ from .engine import GradSync
 from .runtime import default_context
 
 _ENGINES: "weakref.WeakKeyDictionary[torch.nn.Module, GradSync]" = weakref.WeakKeyDictionary()
+_GATHER_ENGINES: "weakref.WeakKeyDictionary[torch.nn.Module, GradSync]" = weakref.WeakKeyDictionary()
 _CONFIG = {"bucket_dtype": os.environ.get("B200DDP_BUCKET_DTYPE", "fp32"),
            "algo": os.environ.get("B200DDP_ALGO", "auto")}
 
@@ -32,6 +33,7 @@ def configure(bucket_dtype=None, algo=None):
             raise ValueError(f"algo must be one of {sorted(_lib.ALGO_NAMES)}")
         _CONFIG["algo"] = algo
     _ENGINES.clear()
+    _GATHER_ENGINES.clear()
 
 
 def dist_init(world_size, rank, master_addr="localhost", master_port="12355"):
@@ -59,12 +61,46 @@ def get_world_size():
     return dist.get_world_size() if dist.is_initialized() else 1
 
 
-def init_parameters(model):
-    """codes/task2/dist_utils.py:33-37: rank 0's parameters to every rank
-    (parameters only - buffers are not broadcast, exactly as in the reference)."""
+def broadcast_from_rank0(tensors):
+    """Rank 0's values of `tensors` to every rank, as flat buckets: rank 0 packs them into
+    its staging area, the other ranks unpack straight out of rank 0's memory over NVLink
+    (one pack + one unpack per bucket instead of one NCCL broadcast per tensor).
+    fp32 CUDA tensors take this path; anything else (e.g. BatchNorm's int64
+    num_batches_tracked) falls back to torch.distributed.broadcast."""
+    from .engine import split_buckets
+    ctx = default_context()
+    flat = [t for t in tensors if t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()]
+    flat_ids = {id(t) for t in flat}
+    for t in tensors:
+        if id(t) not in flat_ids:
+            dist.broadcast(t, 0)
+    if not flat:
+        return
+    numels = [t.numel() for t in flat]
+    for lo, hi, off, _ in split_buckets(numels, 4, None, ctx.staging_bytes):
+        plan = ctx.plan(numels[lo:hi])
+        ptrs = [t.data_ptr() for t in flat[lo:hi]]
+        if ctx.rank == 0:
+            ctx.pack_scale(plan, ptrs, ctx.bucket_ptr(off), 1.0)
+        torch.cuda.synchronize()
+        dist.barrier()                      # rank 0's bucket is complete and visible
+        if ctx.rank != 0:
+            ctx.unpack(plan, ctx.peer_bucket_ptr(0, off), ptrs, 1.0)
+        torch.cuda.synchronize()
+        dist.barrier()                      # everyone has read it; the staging area may be reused
+        plan.close()
+
+
+def init_parameters(model, buffers=False):
+    """codes/task2/dist_utils.py:33-37: rank 0's parameters to every rank.  Like the
+    reference, parameters only by default - the reference does not broadcast buffers
+    (BatchNorm running statistics), which only stays harmless while every rank builds the
+    model from the same seed; buffers=True sends them too."""
     if get_world_size() > 1:
-        for param in model.parameters():
-            dist.broadcast(param.data, 0)
+        tensors = [p.data for p in model.parameters()]
+        if buffers:
+            tensors += [b.data for b in model.buffers()]
+        broadcast_from_rank0(tensors)
 
 
 def engine_for(model) -> GradSync:
@@ -89,6 +125,17 @@ def allreduce_average_gradients(model):
         eng.pending = True
         return
     eng.sync()
+    _straggle()
+
+
+def _straggle():
+    """The lab's bottleneck-node experiment (sections/task2.tex:19; the commented-out
+    time.sleep(0.1) on rank 1 at codes/task2/model-mp.py:47,64-65):
+    B200DDP_STRAGGLER_RANK=r B200DDP_STRAGGLER_MS=t delays rank r by t ms after each sync."""
+    r = os.environ.get("B200DDP_STRAGGLER_RANK")
+    if r is not None and int(r) == get_local_rank():
+        import time
+        time.sleep(float(os.environ.get("B200DDP_STRAGGLER_MS", "100")) / 1e3)
 
 
 def average_gradients(model):
@@ -97,11 +144,48 @@ def average_gradients(model):
 
 
 def allgather_average_gradients(model):
-    """codes/task2/dist_utils.py:44-49 as it was meant: the mean over ranks.  The
-    reference version aliases one tensor for every slot of its gather list and
-    hard-codes two ranks, so it returns the last rank's gradient; that bug is
-    not reproduced."""
-    allreduce_average_gradients(model)
+    """codes/task2/dist_utils.py:44-49 as it was meant: every rank gathers every rank's
+    gradient and averages locally.  On NVLink that is the one-shot kernel (each GPU reads all
+    N buckets, (N-1) x S inbound) - the all-reduce variant above moves 2 (N-1)/N x S - so the
+    lab's AllReduce-vs-AllGather cost comparison (sections/checking.tex:20-22) is
+    allreduce_average_gradients vs this.  The reference version aliases one tensor for every
+    slot of its gather list and hard-codes two ranks, so it returns the last rank's gradient;
+    that bug is not reproduced."""
+    eng = _GATHER_ENGINES.get(model)
+    if eng is None:
+        eng = _GATHER_ENGINES[model] = GradSync(list(model.parameters()), default_context(),
+                                                bucket_dtype=_CONFIG["bucket_dtype"], algo="oneshot")
+    eng.sync()
+    _straggle()
+
+
+class CommTimer:
+    """Accumulated device time of the gradient sync, measured with CUDA events on the
+    current stream as the handbook recommends (sections/task2.tex:71-80), in place of the
+    wall-clock timer of codes/task2/model-mp.py:61-66,79 (which only times the enqueue).
+
+        timer = b200ddp.CommTimer()
+        with timer: dist_utils.allreduce_average_gradients(model)
+        print("Total communication time:", timer.total_seconds())
+    """
+
+    def __init__(self):
+        self._pairs = []
+
+    def __enter__(self):
+        self._a = torch.cuda.Event(enable_timing=True)
+        self._a.record()
+        return self
+
+    def __exit__(self, *exc):
+        b = torch.cuda.Event(enable_timing=True)
+        b.record()
+        self._pairs.append((self._a, b))
+        return False
+
+    def total_seconds(self) -> float:
+        torch.cuda.synchronize()
+        return sum(a.elapsed_time(b) for a, b in self._pairs) * 1e-3
 
 
 def enable_fused_step(model, optimizer, write_grads=True):

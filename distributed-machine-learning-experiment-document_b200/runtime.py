@@ -151,6 +151,12 @@ class Context:
     def bucket_ptr(self, offset_bytes: int) -> int:
         return self.staging_ptr + int(offset_bytes)
 
+    def peer_bucket_ptr(self, peer: int, offset_bytes: int) -> int:
+        """Address, in this process, of rank `peer`'s staging area + offset."""
+        p = c_void_p()
+        check(_lib.lib().b200ddp_peer_staging(self.handle, int(peer), byref(p)), "peer_staging")
+        return int(p.value) + int(offset_bytes)
+
     # ---- kernels ---------------------------------------------------------------
     def pack_scale(self, plan: Plan, grad_ptrs, bucket_ptr: int, scale: float, stream=None):
         check(_lib.lib().b200ddp_pack_scale(self.handle, plan.handle, ptr_array(grad_ptrs), c_void_p(bucket_ptr),

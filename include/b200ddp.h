@@ -50,6 +50,10 @@ int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200dd
 int b200ddp_destroy(b200ddp_ctx *ctx);
 int b200ddp_staging(b200ddp_ctx *ctx, void **ptr, size_t *bytes);
 int b200ddp_flags(b200ddp_ctx *ctx, void **ptr);
+/* this process's mapping of rank `peer`'s staging area (after the peers are opened); used by
+ * the flat initial-weight broadcast that replaces init_parameters, codes/task2/dist_utils.py:33-37:
+ * rank 0 packs, the others unpack straight out of rank 0's memory over NVLink. */
+int b200ddp_peer_staging(b200ddp_ctx *ctx, int peer, void **ptr);
 
 /* NCCL baseline collective: rank 0 makes the id, every rank joins (collective). */
 int b200ddp_nccl_unique_id(void *out_uid /* B200DDP_NCCL_UID_BYTES */);

@@ -235,7 +235,79 @@ def _graph_step(rank, ws, algo):
     assert torch.equal(mine, outs[1]), "ranks diverged"
 
 
+def _next_rows(rank, ws):
+    """flat initial-weight broadcast (with and without buffers), the
+    all-gather aggregation variant, the CUDA-event comm timer, both sampler modes."""
+    import b200ddp
+    du = b200ddp.dist_utils
+
+    def build(seed):
+        torch.manual_seed(seed)
+        return torch.nn.Sequential(torch.nn.Conv2d(1, 8, 3), torch.nn.BatchNorm2d(8), torch.nn.ReLU(),
+                                   torch.nn.Flatten(), torch.nn.Linear(8 * 26 * 26, 10)).cuda()
+
+    def same_everywhere(t):
+        ref = t.detach().clone()
+        torch.distributed.broadcast(ref, 0)
+        return torch.equal(ref, t.detach())
+
+    # (f1) init_parameters: parameters only, exactly like the reference ...
+    m = build(10 + rank)
+    with torch.no_grad():
+        m[1].running_mean.fill_(float(rank))
+    du.init_parameters(m)
+    assert all(same_everywhere(p) for p in m.parameters())
+    assert float(m[1].running_mean[0]) == float(rank)          # buffers untouched (codes/task2/dist_utils.py:35-37)
+    # ... and the fixed variant that also sends buffers (fp32 through the flat path, int64 through torch)
+    m = build(20 + rank)
+    with torch.no_grad():
+        m[1].running_mean.fill_(float(rank))
+        m[1].num_batches_tracked.fill_(rank)
+    du.init_parameters(m, buffers=True)
+    assert all(same_everywhere(t) for t in list(m.parameters()) + list(m.buffers()))
+    assert float(m[1].running_mean[0]) == 0.0 and int(m[1].num_batches_tracked) == 0
+
+    # (f3) all-gather-then-mean aggregation == the mean over ranks, and the comm timer
+    gen = torch.Generator(device="cuda").manual_seed(50 + rank)
+    for p in m.parameters():
+        p.grad = torch.randn(p.shape, device="cuda", generator=gen) * 1e-2
+    want = []
+    for p in m.parameters():
+        parts = [torch.empty_like(p.grad) for _ in range(ws)]
+        torch.distributed.all_gather(parts, p.grad)
+        acc = parts[0].clone()
+        for t in parts[1:]:
+            acc += t
+        want.append(acc / ws)
+    timer = b200ddp.CommTimer()
+    with timer:
+        du.allgather_average_gradients(m)
+    assert timer.total_seconds() > 0
+    for p, w in zip(m.parameters(), want):
+        if ws <= 2:
+            assert torch.equal(p.grad, w)
+        else:
+            assert (p.grad - w).abs().max() <= 1e-5 * w.abs().max()
+
+    # (f2) sampler modes of the lab: random partition (shared seed, disjoint shards) and random sampling
+    class DS:
+        def __len__(self):
+            return 1000
+    part = list(b200ddp.MySampler(DS(), ws, rank, shuffle=True, seed=0))
+    gathered = [None] * ws
+    torch.distributed.all_gather_object(gathered, part)
+    flat = [i for shard in gathered for i in shard]
+    assert sorted(set(flat)) == list(range(1000)) and len(flat) == -(-1000 // ws) * ws
+    samp = list(b200ddp.MySampler(DS(), ws, rank, shuffle=True, seed=rank, mode="sampling"))   # codes/task3/model.py:111
+    want_s = torch.randperm(1000, generator=torch.Generator().manual_seed(rank))[: -(-1000 // ws)].tolist()
+    assert samp == want_s
+
+
 # ------------------------------------------------------------------ tests
+def test_next_rows_two_ranks():
+    _run(2, _next_rows)
+
+
 @pytest.mark.parametrize("algo", ["oneshot", "twoshot", "nccl"])
 def test_graphed_step_two_ranks(algo):
     _run(2, _graph_step, algo)
