@@ -552,20 +552,20 @@ def gpu_arm(args):
                 extras["kernels_error"] = str(e)
     if world > 1:
         dist.barrier()
-    bytes_per_elem = 20 if world == 1 else (24 if bucket_dtype == "fp32" else 22)
-    kern = extras.get("kernels", {}).get("update_direct" if world == 1 else
-                                         ("update_from_bucket_write_grad" if bucket_dtype == "fp32" else "update_from_bf16_bucket"))
+    kern_name = "update_direct" if world == 1 else (
+        "update_from_bucket_write_grad" if bucket_dtype == "fp32" else "update_from_bf16_bucket")
+    kern = extras.get("kernels", {}).get(kern_name)
     traffic = None
-    try:
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "update_kernel_traffic.json"))).get(args.model)
-    except (OSError, ValueError):
+    try:        # ncu's dram__bytes_read.sum + dram__bytes_write.sum per launch of exactly this kernel variant
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "update_kernel_traffic.json"))).get(args.model, {}).get(kern_name)
+    except (OSError, ValueError, AttributeError):
         pass
     roofline = None
     if kern:
-        roofline = {"bound": "hbm", "kernel": "update_kernel (K3 unpack + momentum-SGD)",
+        roofline = {"bound": "hbm", "kernel": f"update_kernel (K3 unpack + momentum-SGD), variant {kern_name}",
                     "achieved": kern["gbs"], "peak": peak_gbs, "peak_source": peak_src, "unit": "GB/s",
                     "frac": kern["gbs"] / peak_gbs, "traffic": traffic,
-                    "algorithmic_bytes_per_launch": bytes_per_elem * P if world > 1 else 20 * P,
+                    "algorithmic_bytes_per_launch": kern["algorithmic_bytes"],
                     "launch_us": kern["us"],
                     "how": "CUDA events around 12 back-to-back launches rotating over 3 disjoint operand sets "
                            "(each launch reads data colder than L2), median of 5 rounds",
