@@ -46,6 +46,8 @@ int sgd_scalars(const b200ddp_sgd_args *a, SgdScalars *o) {
     o->one_minus_damp = (float)(1.0 - a->dampening);
     o->weight_decay = (float)a->weight_decay;
     o->divisor = (float)a->grad_divisor;
+    o->div_rcp = 1.0f / o->divisor;
+    o->div_fast = fast_divisor(o->divisor) ? 1 : 0;
     o->use_div = a->grad_divisor != 1.0;
     o->nesterov = a->nesterov != 0;
     o->maximize = a->maximize != 0;

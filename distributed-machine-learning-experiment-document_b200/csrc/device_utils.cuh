@@ -85,6 +85,25 @@ template <> struct Bucket<__nv_bfloat16> {
     static __device__ __forceinline__ void store1(__nv_bfloat16 *p, float v) { *p = __float2bfloat16_rn(v); }
 };
 
+// ---- x / d, correctly rounded ----------------------------------------------------------
+// `param.grad.data /= world_size` (codes/task2/dist_utils.py:42) is an IEEE division, and for
+// world sizes that are not powers of two it cannot be folded into an exact pre-scale.
+// __fdiv_rn costs ~50 instructions per element and makes the kernel issue-bound (ncu, round 1:
+// unpack 27 us vs pack 14 us for the same bytes).  For a divisor known on the host, Markstein's
+// sequence gives the same correctly rounded quotient in three: q = RN(x * rcp), r = fma(-d, q, x)
+// (exact), q' = fma(r, rcp, q), valid while quotient and remainder stay in the normal range.
+__device__ __forceinline__ float div_rn(float x, float d, float rcp, int fast) {
+    if (fast) {
+        const float ax = fabsf(x);
+        if (ax > 1e-30f && ax < 1e30f) {
+            const float q = __fmul_rn(x, rcp);
+            return __fmaf_rn(__fmaf_rn(-d, q, x), rcp, q);
+        }
+        if (ax == 0.0f) return x;          // +-0 / d = +-0
+    }
+    return __fdiv_rn(x, d);
+}
+
 // ---- momentum SGD on one element ------------------------------------------------
 // Rounding sequence of torch/optim/sgd.py:322-380 on fp32 tensors, where every
 // add_(x, alpha=a) / add(x, alpha=a) is a single fused multiply-add and mul_ is
@@ -92,7 +111,7 @@ template <> struct Bucket<__nv_bfloat16> {
 // sync (codes/task2/dist_utils.py:41-42): the averaged gradient, before the
 // optimizer's own weight-decay / maximize transforms (those are out of place).
 __device__ __forceinline__ void sgd_elem(float g, float &p, float &m, float &g_avg, const SgdScalars &hp) {
-    if (hp.use_div) g = __fdiv_rn(g, hp.divisor);
+    if (hp.use_div) g = div_rn(g, hp.divisor, hp.div_rcp, hp.div_fast);
     g_avg = g;
     if (hp.maximize) g = -g;
     if (hp.has_wd) g = __fmaf_rn(hp.weight_decay, p, g);

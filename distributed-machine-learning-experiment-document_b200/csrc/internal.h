@@ -68,8 +68,14 @@ template <int CAP, int NK> struct TensorTab {
 
 struct SgdScalars {   // host-side casts follow torch: scalars are cast to fp32 once
     float neg_lr, momentum, one_minus_damp, weight_decay, divisor;
+    float div_rcp;        // RN(1 / divisor)
+    int div_fast;         // divisor is a small integer: 3-instruction correctly rounded quotient (device_utils.cuh)
     int use_div, nesterov, maximize, first_step, has_momentum, has_wd;
 };
+
+// Divisors for which the short division sequence was checked bit for bit against IEEE division
+// (every integer 2..64, tests/test_host_logic.py); world sizes are in this range.
+inline bool fast_divisor(float d) { return d >= 2.0f && d <= 64.0f && d == (float)(int)d; }
 
 struct PeerTable {    // kernel parameter of the P2P kernels
     char *staging[B200DDP_MAX_WORLD];

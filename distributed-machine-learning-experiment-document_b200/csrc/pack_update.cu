@@ -43,8 +43,10 @@ __device__ __forceinline__ float4 scale4(float4 v, float s) {
     v.x = __fmul_rn(v.x, s); v.y = __fmul_rn(v.y, s); v.z = __fmul_rn(v.z, s); v.w = __fmul_rn(v.w, s);
     return v;
 }
-__device__ __forceinline__ float4 div4(float4 v, float d) {
-    v.x = __fdiv_rn(v.x, d); v.y = __fdiv_rn(v.y, d); v.z = __fdiv_rn(v.z, d); v.w = __fdiv_rn(v.w, d);
+struct Divisor { float d, rcp; int fast, use; };
+__device__ __forceinline__ float4 div4(float4 v, const Divisor &dv) {
+    v.x = div_rn(v.x, dv.d, dv.rcp, dv.fast); v.y = div_rn(v.y, dv.d, dv.rcp, dv.fast);
+    v.z = div_rn(v.z, dv.d, dv.rcp, dv.fast); v.w = div_rn(v.w, dv.d, dv.rcp, dv.fast);
     return v;
 }
 __device__ __forceinline__ int vec_offset(int u, int tid) { return u * (kThreads * kVec) + tid * kVec; }
@@ -80,7 +82,7 @@ __global__ void __launch_bounds__(kThreads) pack_kernel(const __grid_constant__ 
 template <typename BT, int CAP>
 __global__ void __launch_bounds__(kThreads) unpack_kernel(const __grid_constant__ TensorTab<CAP, 1> tab,
                                                           const Chunk *__restrict__ chunks, int nchunks,
-                                                          const BT *__restrict__ bucket, float divisor, int use_div) {
+                                                          const BT *__restrict__ bucket, Divisor dv) {
     const int tid = threadIdx.x;
     for (int c = blockIdx.x; c < nchunks; c += gridDim.x) {
         const ChunkCtx cc = chunk_ctx(tab, chunks, c);
@@ -92,16 +94,16 @@ __global__ void __launch_bounds__(kThreads) unpack_kernel(const __grid_constant_
 #pragma unroll
             for (int u = 0; u < kUnroll; ++u) v[u] = Bucket<BT>::load4(b + vec_offset(u, tid));
 #pragma unroll
-            for (int u = 0; u < kUnroll; ++u) st_f4(g + vec_offset(u, tid), use_div ? div4(v[u], divisor) : v[u]);
+            for (int u = 0; u < kUnroll; ++u) st_f4(g + vec_offset(u, tid), dv.use ? div4(v[u], dv) : v[u]);
         } else {
             const int nvec = aligned ? cc.count / kVec : 0;
             for (int i = tid; i < nvec; i += kThreads) {
                 const float4 x = Bucket<BT>::load4(b + i * kVec);
-                st_f4(g + i * kVec, use_div ? div4(x, divisor) : x);
+                st_f4(g + i * kVec, dv.use ? div4(x, dv) : x);
             }
             for (int i = nvec * kVec + tid; i < cc.count; i += kThreads) {
                 const float x = Bucket<BT>::load1(b + i);
-                g[i] = use_div ? __fdiv_rn(x, divisor) : x;
+                g[i] = dv.use ? div_rn(x, dv.d, dv.rcp, dv.fast) : x;
             }
         }
     }
@@ -216,8 +218,9 @@ void run_unpack(const b200ddp_plan *plan, const Segment &sg, const void *bucket,
     const void *const *kinds[1] = {grads_out};
     fill_tab(tab, plan, sg, kinds);
     const int n = sg.c1 - sg.c0;
+    const Divisor dv{divisor, 1.0f / divisor, fast_divisor(divisor) ? 1 : 0, divisor != 1.0f ? 1 : 0};
     unpack_kernel<BT, CAP><<<grid_for(unpack_kernel<BT, CAP>, occ, n, sm), kThreads, 0, s>>>(
-        tab, plan->d_chunks + sg.c0, n, (const BT *)bucket, divisor, divisor != 1.0f);
+        tab, plan->d_chunks + sg.c0, n, (const BT *)bucket, dv);
 }
 template <typename BT, bool FB, bool WG, int CAP>
 void run_update(const b200ddp_plan *plan, const Segment &sg, const void *bucket, const PtrArrays &pa,

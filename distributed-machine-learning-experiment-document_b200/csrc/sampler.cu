@@ -21,6 +21,10 @@
 //
 // One cooperative launch; rounds are separated by a grid barrier on a global
 // counter.  All cross-block data is read with ld.cg (L2), never from L1.
+#include <cooperative_groups.h>
+
+#include <cstdlib>
+
 #include "internal.h"
 
 namespace b200ddp {
@@ -84,7 +88,7 @@ __device__ void mt_targets(uint32_t *ring, uint32_t seed, uint32_t n, uint32_t *
             const uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);
             const uint32_t x = c ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
             ring[(k + kMtN) & (kRing - 1)] = x;
-            tgt[k] = k + mt_temper(x) % (n - k);
+            tgt[k] = mt_temper(x);   // raw draw; `% (n - k)` is off this serial path (done in parallel later)
         }
         __syncthreads();
     }
@@ -113,6 +117,8 @@ __global__ void __launch_bounds__(kSamplerThreads) sampler_shuffle_kernel(Sample
 
     // ---- rounds of reserve / commit over the n-1 iterates
     const uint32_t niter = n - 1;
+    // draw -> swap target, in parallel; iterate i is only ever touched by this same thread
+    for (uint32_t i = gtid; i < niter; i += nthreads) sc.tgt[i] = i + __ldcg(sc.tgt + i) % (n - i);
     bool overflow = false;
     for (uint32_t round = 1;; ++round) {
         if (round >= (uint32_t)kMaxRounds) { overflow = true; break; }
@@ -157,6 +163,136 @@ __global__ void __launch_bounds__(kSamplerThreads) sampler_shuffle_kernel(Sample
     }
 }
 
+// ---- n <= 65,535: the same rounds inside one thread-block cluster
+//
+// The rounds above are latency chains: ~37 of them at n = 60,000 (the reference's MNIST case), each
+// paying a software grid barrier (~2 us) and three dependent L2 round trips - 230 us in all, no better
+// than the host.  For short lists one cluster of 8 CTAs is enough parallelism, and then the round
+// barrier is the hardware cluster barrier and every thread keeps its <= 8 iterates (swap target,
+// pending bit) in registers.  Permutation and reservation words stay in global memory (L2).
+// Measured dead end: keeping them in distributed shared memory instead is SLOWER (309 us): DSMEM
+// sustains ~20 B/cycle/SM, and ~120,000 random 4-byte remote atomics per round saturate it.
+constexpr int kClusterCtas = 8;
+constexpr int kClusterMaxN = 65535;
+constexpr int kClusterIters = (kClusterMaxN + kClusterCtas * kSamplerThreads - 1) / (kClusterCtas * kSamplerThreads);   // 8
+
+__device__ __forceinline__ void bar_sync_256() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+// Warps 0-7 of block 0 only (the other warps go straight to the cluster barrier).
+__device__ void mt_targets_256(uint32_t *ring, uint32_t seed, uint32_t n, uint32_t *tgt) {
+    const int tid = threadIdx.x;
+    if (tid == 0) {
+        uint32_t s = seed;
+        ring[0] = s;
+        for (int i = 1; i < kMtN; ++i) {
+            s = 1812433253u * (s ^ (s >> 30)) + (uint32_t)i;
+            ring[i] = s;
+        }
+    }
+    bar_sync_256();
+    const uint32_t ndraw = n - 1;
+    for (uint32_t base = 0; base < ndraw; base += kMtPar) {
+        const uint32_t k = base + tid;
+        if (tid < kMtPar && k < ndraw) {
+            const uint32_t a = ring[k & (kRing - 1)], b = ring[(k + 1) & (kRing - 1)], c = ring[(k + kMtM) & (kRing - 1)];
+            const uint32_t y = (a & 0x80000000u) | (b & 0x7fffffffu);
+            const uint32_t x = c ^ (y >> 1) ^ ((y & 1u) ? 0x9908b0dfu : 0u);
+            ring[(k + kMtN) & (kRing - 1)] = x;
+            tgt[k] = mt_temper(x);   // raw draw; `% (n - k)` is off this serial path (done in parallel later)
+        }
+        bar_sync_256();
+    }
+}
+
+__global__ void __cluster_dims__(kClusterCtas, 1, 1) __launch_bounds__(kSamplerThreads)
+sampler_cluster_kernel(uint32_t *draws, uint32_t *resv, int32_t *perm, uint32_t n, uint32_t seed, int world, int rank,
+                       int64_t num_samples, int64_t *__restrict__ out) {
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    __shared__ uint32_t ring[kRing];
+    __shared__ unsigned int pend[4];                                   // block 0's copy is the cluster's
+    const unsigned int cta = cluster.block_rank();
+    const unsigned int tid = threadIdx.x;
+    const unsigned int nthreads = kClusterCtas * kSamplerThreads;
+    const unsigned int gtid = cta * kSamplerThreads + tid;
+
+    for (uint32_t pos = gtid; pos < n; pos += nthreads) {
+        __stcg(perm + pos, (int32_t)pos);
+        __stcg(resv + pos, 0u);
+    }
+    if (tid < 4) pend[tid] = 0u;
+    if (cta == 0 && tid < 256) mt_targets_256(ring, seed, n, draws);
+    cluster.sync();
+
+    const uint32_t niter = n - 1;
+    uint32_t tg[kClusterIters];
+    unsigned int mask = 0;
+#pragma unroll
+    for (int k = 0; k < kClusterIters; ++k) {
+        const uint32_t i = gtid + k * nthreads;
+        tg[k] = 0;
+        if (i < niter) {
+            tg[k] = i + __ldcg(draws + i) % (n - i);
+            mask |= 1u << k;
+        }
+    }
+    unsigned int *pend0 = cluster.map_shared_rank(pend, 0);
+
+    for (uint32_t round = 1;; ++round) {
+#pragma unroll
+        for (int k = 0; k < kClusterIters; ++k)
+            if (mask & (1u << k)) {
+                const uint32_t i = gtid + k * nthreads;
+                const uint32_t key = (round << 16) | (0xffffu - i);
+                atomicMax(resv + i, key);
+                if (tg[k] != i) atomicMax(resv + tg[k], key);
+            }
+        cluster.sync();
+        if (round > 1 && *reinterpret_cast<volatile unsigned int *>(pend0 + ((round - 1) & 3)) == 0u) break;
+        if (cta == 0 && tid == 0) pend[(round + 1) & 3] = 0u;   // the slot the NEXT round will count into
+        // all of this thread's checks in flight together, then all of its swaps: two L2 round trips
+        // per round instead of two per iterate
+        uint32_t ri[kClusterIters], rt[kClusterIters];
+#pragma unroll
+        for (int k = 0; k < kClusterIters; ++k)
+            if (mask & (1u << k)) {
+                ri[k] = __ldcg(resv + gtid + k * nthreads);
+                rt[k] = __ldcg(resv + tg[k]);
+            }
+        unsigned int win = 0;
+#pragma unroll
+        for (int k = 0; k < kClusterIters; ++k)
+            if (mask & (1u << k)) {
+                const uint32_t key = (round << 16) | (0xffffu - (gtid + k * nthreads));
+                if (ri[k] == key && rt[k] == key) win |= 1u << k;
+            }
+        int32_t pa[kClusterIters], pb[kClusterIters];
+#pragma unroll
+        for (int k = 0; k < kClusterIters; ++k)
+            if ((win & (1u << k)) && tg[k] != gtid + k * nthreads) {
+                pa[k] = __ldcg(perm + gtid + k * nthreads);
+                pb[k] = __ldcg(perm + tg[k]);
+            }
+#pragma unroll
+        for (int k = 0; k < kClusterIters; ++k)
+            if ((win & (1u << k)) && tg[k] != gtid + k * nthreads) {
+                __stcg(perm + gtid + k * nthreads, pb[k]);
+                __stcg(perm + tg[k], pa[k]);
+            }
+        mask &= ~win;
+        const unsigned int mine = mask;
+        const int waiting = __syncthreads_count(mine != 0);
+        if (tid == 0 && waiting) atomicAdd(pend0 + (round & 3), (unsigned int)waiting);
+        // as in the grid version, no barrier here: running ahead only causes spurious retries
+    }
+
+    for (int64_t k = gtid; k < num_samples; k += nthreads) {
+        const uint32_t src = (uint32_t)padded_source((int64_t)rank + (int64_t)world * k, (int64_t)n);
+        out[k] = (int64_t)__ldcg(perm + src);
+    }
+    cluster.sync();   // block 0's `pend` may still be read by the others until here
+}
+
 __global__ void sampler_sequential_kernel(int64_t n, int world, int rank, int64_t num_samples, int64_t *__restrict__ out) {
     for (int64_t k = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; k < num_samples; k += (int64_t)gridDim.x * blockDim.x)
         out[k] = padded_source((int64_t)rank + (int64_t)world * k, n);
@@ -184,6 +320,15 @@ SamplerScratch carve_scratch(void *base, int64_t n) {
 int launch_sampler_on(void *scratch, int sm_count, int64_t n, int world, int rank, uint64_t seed, int64_t num_samples,
                       int64_t *out_dev, cudaStream_t s) {
     SamplerScratch sc = carve_scratch(scratch, n);
+    uint32_t n32 = (uint32_t)n, seed32 = (uint32_t)(seed & 0xffffffffu);   // mt19937 uses the low 32 bits
+    if (n <= kClusterMaxN && !getenv("B200DDP_SAMPLER_NO_CLUSTER")) {
+        // one cluster of 8 CTAs; sc.tgt carries the draws, sc.resv is used as 32-bit words
+        cudaGetLastError();
+        sampler_cluster_kernel<<<kClusterCtas, kSamplerThreads, 0, s>>>(sc.tgt, reinterpret_cast<uint32_t *>(sc.resv), sc.perm,
+                                                                        n32, seed32, world, rank, num_samples, out_dev);
+        B2_CHECK_CUDA(cudaGetLastError());
+        return B200DDP_OK;
+    }
     int per_sm = 0;
     B2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, sampler_shuffle_kernel, kSamplerThreads, 0));
     B2_REQUIRE(per_sm >= 1, B200DDP_ESTATE, "sampler kernel does not fit on an SM");
@@ -192,7 +337,6 @@ int launch_sampler_on(void *scratch, int sm_count, int64_t n, int world, int ran
     if (grid > sm_count * per_sm) grid = sm_count * per_sm;
     if (grid > sm_count) grid = sm_count;   // one block per SM keeps the barrier cheap
     B2_CHECK_CUDA(cudaMemsetAsync(sc.barrier, 0, sizeof(unsigned int), s));
-    uint32_t n32 = (uint32_t)n, seed32 = (uint32_t)(seed & 0xffffffffu);   // mt19937 uses the low 32 bits
     void *params[] = {&sc, &n32, &seed32, &world, &rank, &num_samples, &out_dev};
     B2_CHECK_CUDA(cudaLaunchCooperativeKernel((const void *)sampler_shuffle_kernel, dim3(grid), dim3(kSamplerThreads),
                                               params, 0, s));

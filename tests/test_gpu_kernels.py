@@ -339,3 +339,21 @@ def test_empty_plan_is_a_noop(ctx1):
     ctx1.pack_scale(plan, [], ctx1.bucket_ptr(0), 1.0)
     ctx1.unpack_sgd(plan, ctx1.bucket_ptr(0), [], None, None, b200ddp.sgd_args(0.1))
     assert plan.bucket_elems == 0
+
+
+@pytest.mark.parametrize("divisor", [3.0, 5.0, 6.0, 7.0, 2.5])
+def test_division_edge_values_match_ieee(ctx1, divisor):
+    """The short division sequence (small integer divisors) and its __fdiv_rn fallback (everything
+    else: zeros, denormals, huge values, non-integer divisors) both give the IEEE quotient."""
+    rng = np.random.default_rng(3)
+    n = 70001
+    x = (rng.standard_normal(n) * 10.0 ** rng.integers(-44, 38, n)).astype(np.float32)
+    x[:12] = np.float32([0.0, -0.0, 1e-45, -1e-45, 1.1754944e-38, 3.4e38, -3.4e38, 1e-30, 1e30, 1.0, 3.0, 7.0])
+    plan = ctx1.plan((n,))
+    src, out = to_dev([x])[0], torch.empty(n, device=dev())
+    ctx1.pack_scale(plan, [src.data_ptr()], ctx1.bucket_ptr(0), 1.0)
+    ctx1.unpack(plan, ctx1.bucket_ptr(0), [out.data_ptr()], divisor)
+    got = out.cpu().numpy()
+    with np.errstate(all="ignore"):
+        want = (x / np.float32(divisor)).astype(np.float32)
+    assert np.array_equal(got.view(np.uint32), want.view(np.uint32))          # bit patterns, so that -0 and denormals count

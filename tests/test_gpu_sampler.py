@@ -115,3 +115,21 @@ def test_public_sampler_classes_match_torch(ctx1):
         assert sum(len(b) for b in loader) == 2502
     finally:
         b200ddp.runtime._default = None
+
+
+def test_cluster_and_grid_kernels_agree(ctx1):
+    """n <= 65,535 runs in one thread-block cluster (state in distributed shared memory), larger n
+    in the cooperative grid kernel; B200DDP_SAMPLER_NO_CLUSTER forces the latter.  Both must give
+    torch's permutation."""
+    for n in (1, 2, 8, 9, 1000, 8191, 8192, 8193, 50000, 60000, 65535):
+        for seed in (0, 77):
+            os.environ.pop("B200DDP_SAMPLER_NO_CLUSTER", None)
+            a = _shard(ctx1, n, 1, 0, seed)
+            os.environ["B200DDP_SAMPLER_NO_CLUSTER"] = "1"
+            try:
+                b = _shard(ctx1, n, 1, 0, seed)
+            finally:
+                os.environ.pop("B200DDP_SAMPLER_NO_CLUSTER", None)
+            ref = so.c_randperm(n, seed)
+            assert np.array_equal(a, ref), (n, seed, "cluster")
+            assert np.array_equal(b, ref), (n, seed, "grid")

@@ -170,3 +170,25 @@ def test_oracle_under_gloo_world2(golden_dir):
         assert p.exitcode == 0
     res = dict(q.get() for _ in range(2))
     assert res == {0: True, 1: True}
+
+
+# ------------------------------------------------------------------ short correctly-rounded division
+def test_short_division_is_correctly_rounded():
+    """csrc/device_utils.cuh div_rn: q = RN(x * rcp), r = fma(-d, q, x), q' = fma(r, rcp, q) must equal
+    the IEEE quotient x / d for every integer divisor 2..64 (world sizes), as long as x is in the
+    range the kernel takes the short path for.  fma is emulated through float64 (the product of two
+    fp32 is exact there)."""
+    def fma32(a, b, c):
+        return (a.astype(np.float64) * b.astype(np.float64) + c.astype(np.float64)).astype(np.float32)
+    rng = np.random.default_rng(0)
+    x = np.concatenate([
+        (rng.standard_normal(400_000) * 10.0 ** rng.integers(-25, 25, 400_000)).astype(np.float32),
+        np.arange(0x3F800000, 0x40000000, 37, dtype=np.uint32).view(np.float32),          # a sweep of mantissas
+        np.float32([1e-30, 1.0000001e-30, 9.99e29, 3.0, -3.0, 1.0, 0.1, 7.0, 2.0 ** -20, 4096 * 2.0 ** -20])])
+    x = x[(np.abs(x) > 1e-30) & (np.abs(x) < 1e30)]
+    for d in range(2, 65):
+        dd = np.float32(d)
+        rcp = np.float32(1.0) / dd
+        q = (x * rcp).astype(np.float32)
+        q2 = fma32(fma32(np.full_like(x, -dd), q, x), np.full_like(x, rcp), q)
+        assert np.array_equal(q2, (x / dd).astype(np.float32)), d
