@@ -11,8 +11,9 @@ from ctypes import (POINTER, Structure, byref, c_char_p, c_double, c_float, c_in
                     c_size_t, c_uint64, c_void_p)
 
 F32, BF16 = 0, 1
-ALGO_AUTO, ALGO_NCCL, ALGO_ONESHOT, ALGO_TWOSHOT = 0, 1, 2, 3
-ALGO_NAMES = {"auto": ALGO_AUTO, "nccl": ALGO_NCCL, "oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT}
+ALGO_AUTO, ALGO_NCCL, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3, 4
+ALGO_NAMES = {"auto": ALGO_AUTO, "nccl": ALGO_NCCL, "oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT,
+              "nvls": ALGO_NVLS}
 MAX_WORLD = 8
 IPC_BYTES = 128
 NCCL_UID_BYTES = 128
@@ -47,6 +48,7 @@ _SIGNATURES = {
     "b200ddp_ipc_export": (c_int, [c_void_p, c_void_p]),
     "b200ddp_ipc_open_peers": (c_int, [c_void_p, c_void_p]),
     "b200ddp_set_peers_direct": (c_int, [c_void_p, _PP, _PP]),
+    "b200ddp_adopt_symmetric": (c_int, [c_void_p, _PP, c_void_p, c_size_t]),
     "b200ddp_plan_create": (c_int, [c_void_p, c_int, POINTER(c_int64), c_int, POINTER(c_void_p)]),
     "b200ddp_plan_destroy": (c_int, [c_void_p]),
     "b200ddp_plan_bucket_elems": (c_int64, [c_void_p]),

@@ -3,6 +3,7 @@
 // are in include/b200ddp.h.
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <cmath>
 #include <new>
@@ -139,12 +140,12 @@ int b200ddp_destroy(b200ddp_ctx *ctx) {
     if (ctx->peers_ipc) {
         for (int r = 0; r < ctx->world; ++r) {
             if (r == ctx->rank) continue;
-            if (ctx->peers.staging[r]) cudaIpcCloseMemHandle(ctx->peers.staging[r]);
+            if (ctx->peers.staging[r] && !ctx->staging_external) cudaIpcCloseMemHandle(ctx->peers.staging[r]);
             if (ctx->peers.flags[r]) cudaIpcCloseMemHandle(ctx->peers.flags[r]);
         }
     }
     cudaFree(ctx->sampler_scratch);
-    cudaFree(ctx->staging);
+    if (!ctx->staging_external) cudaFree(ctx->staging);
     cudaFree(ctx->flags);
     cudaFree(ctx->block_gen);
     cudaGetLastError();
@@ -244,6 +245,31 @@ int b200ddp_set_peers_direct(b200ddp_ctx *ctx, void *const *staging_ptrs, void *
         ctx->peers.flags[r] = (uint32_t *)flag_ptrs[r];
     }
     ctx->peers_ready = true;
+    return B200DDP_OK;
+}
+
+int b200ddp_adopt_symmetric(b200ddp_ctx *ctx, void *const *peer_ptrs, void *mc_ptr, size_t bytes) {
+    B2_REQUIRE(ctx != nullptr && peer_ptrs != nullptr, B200DDP_EINVAL, "NULL argument");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    B2_REQUIRE(ctx->world > 1, B200DDP_ESTATE, "symmetric memory is for more than one rank");
+    B2_REQUIRE(!ctx->staging_external, B200DDP_ESTATE, "symmetric memory already adopted");
+    B2_REQUIRE(bytes >= 2 * ctx->staging_bytes, B200DDP_EINVAL, "symmetric buffer of %zu bytes is smaller than 2 x %zu",
+               bytes, ctx->staging_bytes);
+    for (int r = 0; r < ctx->world; ++r)
+        B2_REQUIRE(peer_ptrs[r] != nullptr && ((uintptr_t)peer_ptrs[r] & 255) == 0, B200DDP_EINVAL,
+                   "peer buffer %d is NULL or not 256-byte aligned", r);
+    B2_REQUIRE(((uintptr_t)mc_ptr & 255) == 0, B200DDP_EINVAL, "multicast address is not 256-byte aligned");
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    B2_CHECK_CUDA(cudaDeviceSynchronize());
+    if (ctx->peers_ipc)
+        for (int r = 0; r < ctx->world; ++r)
+            if (r != ctx->rank && ctx->peers.staging[r]) cudaIpcCloseMemHandle(ctx->peers.staging[r]);
+    cudaFree(ctx->staging);
+    cudaGetLastError();
+    ctx->staging_external = true;
+    ctx->staging = (char *)peer_ptrs[ctx->rank];
+    for (int r = 0; r < ctx->world; ++r) ctx->peers.staging[r] = (char *)peer_ptrs[r];
+    ctx->mc_ptr = (char *)mc_ptr;
     return B200DDP_OK;
 }
 
@@ -412,6 +438,12 @@ int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype) {
     // reduction wins (727 vs 646 GB/s at 1 GiB).
     const size_t oneshot_max = (size_t)(ctx->world <= 2 ? 1024 : ctx->world <= 4 ? 512 : 256) << 10;
     if (bytes <= oneshot_max) return B200DDP_ALGO_ONESHOT;
+    // In-switch reduction, when a multicast mapping was adopted.  B200DDP_NVLS_MIN_BYTES sets the
+    // size from which it is preferred (unset: never chosen automatically).
+    if (ctx->mc_ptr) {
+        static const long long nvls_min = getenv("B200DDP_NVLS_MIN_BYTES") ? atoll(getenv("B200DDP_NVLS_MIN_BYTES")) : -1;
+        if (nvls_min >= 0 && (long long)bytes >= nvls_min) return B200DDP_ALGO_NVLS;
+    }
     if (ctx->world > 4 && ctx->nccl_comm && bytes > ((size_t)128 << 20)) return B200DDP_ALGO_NCCL;
     return B200DDP_ALGO_TWOSHOT;
 }
@@ -432,8 +464,12 @@ int b200ddp_allreduce(b200ddp_ctx *ctx, size_t offset_bytes, int64_t nelem, int 
         B2_REQUIRE(ctx->nccl_comm != nullptr, B200DDP_ESTATE, "NCCL communicator not initialised");
         return nccl_allreduce(ctx, ctx->staging + offset_bytes, nelem, dtype, s);
     }
-    B2_REQUIRE(algo == B200DDP_ALGO_ONESHOT || algo == B200DDP_ALGO_TWOSHOT, B200DDP_EINVAL, "bad algo %d", algo);
     B2_REQUIRE(ctx->peers_ready, B200DDP_ESTATE, "peer memory not opened");
+    if (algo == B200DDP_ALGO_NVLS) {
+        B2_REQUIRE(ctx->mc_ptr != nullptr, B200DDP_ESTATE, "no multicast mapping: NVLS needs b200ddp_adopt_symmetric");
+        return launch_nvls_allreduce(ctx, offset_bytes, nelem, dtype, s);
+    }
+    B2_REQUIRE(algo == B200DDP_ALGO_ONESHOT || algo == B200DDP_ALGO_TWOSHOT, B200DDP_EINVAL, "bad algo %d", algo);
     if (algo == B200DDP_ALGO_ONESHOT && result_offset_bytes) *result_offset_bytes = ctx->staging_bytes + offset_bytes;
     return launch_p2p_allreduce(ctx, offset_bytes, nelem, dtype, algo, s);
 }

@@ -88,6 +88,8 @@ struct b200ddp_ctx {
     int rank = 0, world = 1, device = 0;
     size_t staging_bytes = 0;          // one half
     char *staging = nullptr;           // 2 x staging_bytes
+    bool staging_external = false;     // adopted symmetric memory: owned by the caller
+    char *mc_ptr = nullptr;            // multicast address over every rank's staging (NVLS), or null
     uint32_t *flags = nullptr;         // peer-visible: kMaxBlocksP2P x MAX_WORLD
     uint32_t *block_gen = nullptr;     // local: barrier generation of each block index, advanced by the kernels
     bool peers_ready = false;
@@ -135,6 +137,7 @@ int launch_update(const b200ddp_plan *plan, const void *bucket /*null: direct*/,
 // p2p.cu
 int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int sm_count);
 int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, int algo, cudaStream_t s);
+int launch_nvls_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, cudaStream_t s);
 int launch_p2p_allreduce_emu(b200ddp_ctx *const *ctxs, int n, size_t off, int64_t nelem, int dtype,
                              int algo, cudaStream_t s);
 int launch_oneshot_update(b200ddp_ctx *ctx, const b200ddp_plan *plan, size_t off, const PtrArrays &pa,

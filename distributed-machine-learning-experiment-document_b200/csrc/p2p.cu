@@ -182,6 +182,69 @@ __global__ void __launch_bounds__(kP2PThreads) twoshot_kernel(P2PArgs a) {
     if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
+// ---- in-switch reduction (NVLink SHARP) ---------------------------------------------
+// mc is a multicast address over every rank's staging: one multimem.ld_reduce makes the switch
+// fetch the 16 bytes from all N GPUs and return their sum (fp32 accumulation), one multimem.st
+// stores to all N.  Rank r handles slice r, like the two-shot kernel, but every GPU receives
+// S/N + S instead of 2 (N-1)/N x S and sends as little.  The order of the additions inside the
+// switch is not specified: results are identical on all ranks (each element is reduced once and
+// broadcast) and exact for N = 2, within the fp32 bound otherwise.
+template <typename BT> struct Multimem;
+template <> struct Multimem<float> {
+    static __device__ __forceinline__ uint4 ld_reduce(const char *p) {
+        uint4 r;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+        return r;
+    }
+    static __device__ __forceinline__ void st(char *p, const uint4 &v) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    }
+};
+template <> struct Multimem<__nv_bfloat16> {
+    static __device__ __forceinline__ uint4 ld_reduce(const char *p) {
+        uint4 r;
+        asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0,%1,%2,%3}, [%4];"
+                     : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w) : "l"(p) : "memory");
+        return r;
+    }
+    static __device__ __forceinline__ void st(char *p, const uint4 &v) {
+        asm volatile("multimem.st.relaxed.sys.global.v4.bf16x2 [%0], {%1,%2,%3,%4};"
+                     :: "l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    }
+};
+
+constexpr int kNvlsUnroll = 4;
+
+template <typename BT>
+__global__ void __launch_bounds__(kP2PThreads) nvls_kernel(P2PArgs a, char *mc) {
+    const int rank = a.rank, world = a.world, bid = blockIdx.x;
+    const uint32_t gen = a.gen[rank][bid];
+    peer_barrier(a.pt, rank, world, bid, gen + 1);
+    const int64_t per = (a.nvec + world - 1) / world;
+    const int64_t lo = per * rank;
+    const int64_t hi = lo + per < a.nvec ? lo + per : a.nvec;
+    const int64_t stride = (int64_t)gridDim.x * kP2PThreads;
+    char *base = mc + a.off_bytes;
+    for (int64_t i0 = lo + (int64_t)bid * kP2PThreads + threadIdx.x; i0 < hi; i0 += stride * kNvlsUnroll) {
+        uint4 v[kNvlsUnroll];
+#pragma unroll
+        for (int u = 0; u < kNvlsUnroll; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < hi) v[u] = Multimem<BT>::ld_reduce(base + i * 16);
+        }
+#pragma unroll
+        for (int u = 0; u < kNvlsUnroll; ++u) {
+            const int64_t i = i0 + u * stride;
+            if (i < hi) Multimem<BT>::st(base + i * 16, v[u]);
+        }
+    }
+    __threadfence_system();   // multimem stores are weak: order them before the barrier's release
+    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
+}
+
 // ---- fused one-shot reduce + update --------------------------------------------
 // Tensor tables come by value in the kernel parameters (see TensorTab); under EMU every
 // emulated rank has its own table and its own chunk list.
@@ -338,6 +401,16 @@ int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype,
     const void *k = pick<false>(dtype, algo, ctx->world);
     void *params[] = {&a};
     B2_CHECK_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kP2PThreads), params, 0, s));
+    return B200DDP_OK;
+}
+
+int launch_nvls_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, cudaStream_t s) {
+    P2PArgs a = make_args(ctx, off, nelem, dtype);
+    const int grid = p2p_grid_for(nelem, dtype, B200DDP_ALGO_TWOSHOT, ctx->world, kSmCount);
+    cudaGetLastError();
+    if (dtype == B200DDP_F32) nvls_kernel<float><<<grid, kP2PThreads, 0, s>>>(a, ctx->mc_ptr);
+    else nvls_kernel<__nv_bfloat16><<<grid, kP2PThreads, 0, s>>>(a, ctx->mc_ptr);
+    B2_LAUNCH_CHECK();
     return B200DDP_OK;
 }
 

@@ -96,6 +96,9 @@ class Context:
         self.flags_ptr = int(f.value)
         self.has_nccl = False
         self.has_peers = self.world == 1
+        self.has_multicast = False
+        self.symmetric_error = None
+        self._symmetric = None                 # (tensor, handle) of adopted torch symmetric memory
         self._plans = weakref.WeakSet()
 
     # ---- set-up --------------------------------------------------------------
@@ -121,7 +124,52 @@ class Context:
             uid = ctypes.create_string_buffer(box[0], _lib.NCCL_UID_BYTES)
             check(_lib.lib().b200ddp_nccl_init(self.handle, uid), "nccl_init")
             self.has_nccl = True
+        if p2p and os.environ.get("B200DDP_SYMMETRIC", "1") != "0":
+            self._adopt_symmetric(group)
         return self
+
+    def _adopt_symmetric(self, group):
+        """Move the staging area into torch symmetric memory, which also yields a multicast
+        address over all ranks' buffers (NVLink SHARP) for the in-switch all-reduce.  Every step
+        is agreed on by all ranks; if anything is missing the CUDA-IPC staging stays in use."""
+        grp = group if group is not None else dist.group.WORLD
+
+        def all_ok(flag):
+            votes = [None] * self.world
+            dist.all_gather_object(votes, bool(flag), group=group)
+            return all(votes)
+
+        tensor = handle = None
+        nbytes = 2 * self.staging_bytes + 256
+        try:
+            import torch.distributed._symmetric_memory as symm
+            tensor = symm.empty(nbytes // 4, dtype=torch.float32, device=torch.device("cuda", self.device))
+        except Exception as e:          # old torch, unsupported driver, ...
+            self.symmetric_error = e
+        if not all_ok(tensor is not None):
+            return
+        try:
+            handle = symm.rendezvous(tensor, grp)
+            tensor.zero_()
+            torch.cuda.synchronize()
+            ptrs = [int(p) for p in handle.buffer_ptrs]
+            assert len(ptrs) == self.world
+            shift = tensor.data_ptr() - ptrs[self.rank]      # the tensor may sit at an offset inside the block
+            assert 0 <= shift and shift % 256 == 0
+            ptrs = [p + shift for p in ptrs]
+            mc = int(getattr(handle, "multicast_ptr", 0) or 0)
+            mc = mc + shift if mc else 0
+        except Exception as e:
+            self.symmetric_error = e
+            handle = None
+        if not all_ok(handle is not None):
+            return
+        check(_lib.lib().b200ddp_adopt_symmetric(self.handle, ptr_array(ptrs), c_void_p(mc) if mc else None, nbytes),
+              "adopt_symmetric")
+        dist.barrier(group=group)       # everyone zeroed and adopted before anyone packs
+        self._symmetric = (tensor, handle)
+        self.staging_ptr = tensor.data_ptr()
+        self.has_multicast = bool(mc)
 
     def link_local(self, peers: "list[Context]"):
         """Same-process peers (one process driving several contexts)."""

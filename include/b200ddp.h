@@ -27,7 +27,8 @@ typedef void *b200ddp_stream;              /* a cudaStream_t                    
 
 enum { B200DDP_F32 = 0, B200DDP_BF16 = 1 };                 /* bucket / wire dtype */
 enum { B200DDP_ALGO_AUTO = 0, B200DDP_ALGO_NCCL = 1,
-       B200DDP_ALGO_ONESHOT = 2, B200DDP_ALGO_TWOSHOT = 3 };
+       B200DDP_ALGO_ONESHOT = 2, B200DDP_ALGO_TWOSHOT = 3,
+       B200DDP_ALGO_NVLS = 4 /* in-switch reduction, needs b200ddp_adopt_symmetric with a multicast address */ };
 enum { B200DDP_OK = 0, B200DDP_EINVAL = -1, B200DDP_ECUDA = -2, B200DDP_ENCCL = -3,
        B200DDP_ESTATE = -4, B200DDP_ETOOBIG = -5 };
 
@@ -66,6 +67,15 @@ int b200ddp_ipc_export(b200ddp_ctx *ctx, void *out /* B200DDP_IPC_BYTES */);
 int b200ddp_ipc_open_peers(b200ddp_ctx *ctx, const void *handles /* world x B200DDP_IPC_BYTES */);
 int b200ddp_set_peers_direct(b200ddp_ctx *ctx, void *const *staging_ptrs, void *const *flag_ptrs);
 
+/* Replace the staging area by caller-provided SYMMETRIC memory: peer_ptrs[r] is this process's
+ * mapping of rank r's buffer (peer_ptrs[rank] the local one), all of `bytes` >= 2 x staging_bytes
+ * and zeroed; mc_ptr (nullable) is a multicast address over the same buffers (NVLink SHARP:
+ * a multimem.ld_reduce on it returns the sum over all ranks, a multimem.st on it stores to all).
+ * The Python side gets these from torch.distributed._symmetric_memory; ownership stays with the
+ * caller, which must keep the memory alive until b200ddp_destroy.  Collective in effect: every
+ * rank must adopt, or none. */
+int b200ddp_adopt_symmetric(b200ddp_ctx *ctx, void *const *peer_ptrs, void *mc_ptr, size_t bytes);
+
 /* ---- plan: bucket layout of a list of T fp32 tensors ------------------------
  * Tensor t occupies bucket elements [offset[t], offset[t] + numel[t]); offsets
  * are aligned to 32 elements, the padding stays zero.  A plan is immutable and
@@ -87,7 +97,7 @@ int b200ddp_pack_scale(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *
 
 /* ---- K2 all-reduce (SUM) of a bucket that lives in this ctx's staging -------
  * Replaces `dist.all_reduce(..., op=SUM)`, codes/task2/dist_utils.py:41.
- * offset_bytes / nelem address the first staging half.  NCCL and two-shot
+ * offset_bytes / nelem address the first staging half.  NCCL, two-shot and NVLS
  * reduce in place; one-shot writes its result into the second half.
  * *result_offset_bytes receives where the sums are, relative to the staging
  * base.  Every rank must make the same calls in the same order.  world == 1

@@ -52,7 +52,8 @@ def main():
                                generator=torch.Generator(device=dev).manual_seed(rank)) * 1e-2)
             plan = ctx.plan([nelem], dtype)
             tbuf = src.to(tdt)
-            algos = ["nccl", "twoshot"] + (["oneshot"] if S <= args.oneshot_max_mb << 20 else []) + ["torch_nccl"]
+            algos = (["nccl", "twoshot"] + (["nvls"] if ctx.has_multicast else []) +
+                     (["oneshot"] if S <= args.oneshot_max_mb << 20 else []) + ["torch_nccl"])
             for algo in algos:
                 # `iters` launches back to back between two events (host launch latency is hidden
                 # once the device is the bottleneck; below that the figure IS the launch rate).
