@@ -438,10 +438,14 @@ int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype) {
     // reduction wins (727 vs 646 GB/s at 1 GiB).
     const size_t oneshot_max = (size_t)(ctx->world <= 2 ? 1024 : ctx->world <= 4 ? 512 : 256) << 10;
     if (bytes <= oneshot_max) return B200DDP_ALGO_ONESHOT;
-    // In-switch reduction, when a multicast mapping was adopted.  B200DDP_NVLS_MIN_BYTES sets the
-    // size from which it is preferred (unset: never chosen automatically).
+    // In-switch reduction, when a multicast mapping was adopted.  Measured on 8 GPUs
+    // (profiles/r01_sweep_n8_nvls_*.jsonl): level with two-shot up to 16 MB, then ahead - 574 vs
+    // 551 GB/s at 64 MB, 768 vs 620 (NCCL 657) at 256 MB, 791 vs 641 (NCCL 720) at 1 GiB.  On 2
+    // GPUs it loses (380 vs 626 GB/s at 256 MB): the switch has nothing to save there.
+    // B200DDP_NVLS_MIN_BYTES overrides the threshold (-1: never).
     if (ctx->mc_ptr) {
-        static const long long nvls_min = getenv("B200DDP_NVLS_MIN_BYTES") ? atoll(getenv("B200DDP_NVLS_MIN_BYTES")) : -1;
+        static const long long nvls_env = getenv("B200DDP_NVLS_MIN_BYTES") ? atoll(getenv("B200DDP_NVLS_MIN_BYTES")) : -2;
+        const long long nvls_min = nvls_env != -2 ? nvls_env : (ctx->world >= 8 ? (24ll << 20) : -1);
         if (nvls_min >= 0 && (long long)bytes >= nvls_min) return B200DDP_ALGO_NVLS;
     }
     if (ctx->world > 4 && ctx->nccl_comm && bytes > ((size_t)128 << 20)) return B200DDP_ALGO_NCCL;
