@@ -290,7 +290,7 @@ def reference_arm(args):
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads * world, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -411,8 +411,9 @@ def gpu_arm(args):
     world = env_int("WORLD_SIZE", 1)
     rank = env_int("RANK", 0)
     local = env_int("LOCAL_RANK", 0)
-    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
-        os.environ["NCCL_DEBUG"] = "WARN"      # keep NCCL's version banner off stdout: one JSON line only
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION", "WARN"):
+        # NCCL prints its version banner to STDOUT at the VERSION and WARN levels: stdout carries one JSON line only
+        os.environ["NCCL_DEBUG"] = "NONE"
     if world != args.gpus and world > 1:
         raise SystemExit(f"--gpus {args.gpus} but WORLD_SIZE={world}")
     if args.gpus > 1 and world == 1:
@@ -591,14 +592,31 @@ def gpu_arm(args):
     line.update(extras)
     if world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_sample(1, name, batch, lr, args.cpu_budget_s)
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The one JSON line, on the real stdout."""
+    sys.stdout.flush()
+    if _REAL_STDOUT is not None:
+        os.dup2(_REAL_STDOUT, 1)
+    print(json.dumps(line), flush=True)
+
+
 def main():
+    global _REAL_STDOUT
     args = parse()
+    # Everything else that any library writes to fd 1 (NCCL's version banner, for one) goes to
+    # stderr: stdout carries exactly one JSON line.
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     if args.impl == "reference":
         return reference_arm(args)
     return gpu_arm(args)
