@@ -48,7 +48,7 @@ def parse():
     ap.add_argument("--model", default="resnet18", choices=sorted(MODELS))
     ap.add_argument("--batch", type=int, default=0, help="per-rank batch (0 = the config's)")
     ap.add_argument("--bucket-dtype", default=None, choices=["fp32", "bf16"])
-    ap.add_argument("--algo", default="auto", choices=["auto", "nccl", "oneshot", "twoshot"])
+    ap.add_argument("--algo", default="auto", choices=["auto", "nccl", "oneshot", "twoshot", "nvls"])
     ap.add_argument("--mode", default="fused", choices=["fused", "strict"],
                     help="fused: sync folded into optimizer.step(); strict: p.grad averaged first")
     ap.add_argument("--step", default="graph", choices=["graph", "eager"],
