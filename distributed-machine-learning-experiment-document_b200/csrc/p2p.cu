@@ -49,13 +49,29 @@ __device__ __forceinline__ void st_peer_u4(void *p, const uint4 &v) {
 // All threads of the block call this.  Orders every earlier write of the block
 // (release, cumulative over the bar.sync) before the flag, and every later read
 // after the peers' flags (acquire, then bar.sync).
+__device__ __forceinline__ unsigned long long global_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// A peer that never arrives (crashed rank, mismatched call sequence) must not hang the GPU for
+// good: after kPeerTimeoutNs the block traps, which fails the launch with an error the host sees.
+constexpr unsigned long long kPeerTimeoutNs = 60ull * 1000 * 1000 * 1000;
+
 __device__ __forceinline__ void peer_barrier(const PeerTable &pt, int rank, int world, int bid, uint32_t gen) {
     __syncthreads();
     if ((int)threadIdx.x < world) {
         const int peer = threadIdx.x;
         st_release_sys(pt.flags[peer] + bid * B200DDP_MAX_WORLD + rank, gen);
         const uint32_t *mine = pt.flags[rank] + bid * B200DDP_MAX_WORLD + peer;
-        while ((int32_t)(ld_acquire_sys(mine) - gen) < 0) {
+        unsigned long long t0 = 0;
+        for (unsigned int spins = 0; (int32_t)(ld_acquire_sys(mine) - gen) < 0; ++spins) {
+            if ((spins & 0xfffu) == 0xfffu) {          // look at the clock every 4096 polls
+                const unsigned long long now = global_ns();
+                if (t0 == 0) t0 = now;
+                else if (now - t0 > kPeerTimeoutNs) __trap();
+            }
         }
     }
     __syncthreads();

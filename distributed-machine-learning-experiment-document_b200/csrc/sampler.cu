@@ -52,8 +52,10 @@ __device__ __forceinline__ void grid_barrier(unsigned int *counter, unsigned int
         const unsigned int target = phase * gridDim.x;
         __threadfence();
         atomicAdd(counter, 1u);
-        while (*reinterpret_cast<volatile unsigned int *>(counter) < target) {
-        }
+        // all blocks are co-resident (cooperative launch), so this terminates; the poll budget only
+        // turns a would-be hang (a bug) into a failed launch
+        for (unsigned long long spins = 0; *reinterpret_cast<volatile unsigned int *>(counter) < target; ++spins)
+            if (spins > (1ull << 27)) __trap();   // about a minute of L2 polls
         __threadfence();
     }
     __syncthreads();
