@@ -77,3 +77,15 @@ def test_product_does_not_import_the_oracle():
             if f.endswith((".py", ".cu", ".cuh", ".h", ".cpp")):
                 text = open(os.path.join(dirpath, f)).read()
                 assert "oracle" not in text.lower(), f"{f} mentions the oracle"
+
+
+def test_header_is_plain_c():
+    """The boundary is a C ABI: the header must compile as C99 (no torch, no C++ in the signatures)."""
+    import subprocess
+    hdr = os.path.join(ROOT, "include", "b200ddp.h")
+    for cmd in (["gcc", "-x", "c", "-std=c99", "-Wall", "-pedantic", "-Werror", "-fsyntax-only", hdr],
+                ["g++", "-x", "c++", "-std=c++11", "-fsyntax-only", hdr]):
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        assert r.returncode == 0, r.stderr
+    text = open(hdr).read()
+    assert "torch" not in re.sub(r"/\*.*?\*/", "", text, flags=re.S)
