@@ -115,11 +115,10 @@ class GradSync:
             return 1.0 / n, 1.0
         return 1.0, float(n)
 
-    def _pack_and_reduce(self, b: _Bucket, fuse_oneshot: bool):
+    def _pack_and_reduce(self, b: _Bucket, grad_ptrs, fuse_oneshot: bool):
         """Returns True if the reduction was left to a fused one-shot update."""
         scale, _ = self._scales()
-        grads = self._grads(b)
-        self.ctx.pack_scale(b.plan, [g.data_ptr() for g in grads], self.ctx.bucket_ptr(b.offset), scale)
+        self.ctx.pack_scale(b.plan, grad_ptrs, self.ctx.bucket_ptr(b.offset), scale)
         self.launches += 1
         b.result_offset = b.offset
         if self.world == 1:
@@ -141,9 +140,9 @@ class GradSync:
             return            # all_reduce over one rank and a division by 1 change nothing
         _, divisor = self._scales()
         for b in self.buckets:
-            self._pack_and_reduce(b, fuse_oneshot=False)
-            grads = self._grads(b)
-            self.ctx.unpack(b.plan, self.ctx.bucket_ptr(b.result_offset), [g.data_ptr() for g in grads], divisor)
+            gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])
+            self._pack_and_reduce(b, gs, fuse_oneshot=False)
+            self.ctx.unpack(b.plan, self.ctx.bucket_ptr(b.result_offset), gs, divisor)
             self.launches += 1
 
     # ---- fused with the optimizer ---------------------------------------------------------
@@ -155,14 +154,15 @@ class GradSync:
         args = sgd_args(first_step=first_step, grad_divisor=divisor, **hyper)
         has_mom = hyper.get("momentum", 0.0) != 0.0
         for b in self.buckets:
-            fused = self._pack_and_reduce(b, fuse_oneshot=True)
+            gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])      # gathered once, used by pack and update
+            fused = self._pack_and_reduce(b, gs, fuse_oneshot=True)
             ps = [p.data_ptr() for p in self.params[b.lo:b.hi]]
             ms = [m.data_ptr() for m in moms[b.lo:b.hi]] if has_mom else None
-            gs = [g.data_ptr() for g in self._grads(b)] if write_grads else None
+            go = gs if write_grads else None
             if fused:
-                self.ctx.allreduce_sgd(b.plan, b.offset, ps, ms, gs, args)
+                self.ctx.allreduce_sgd(b.plan, b.offset, ps, ms, go, args)
             else:
-                self.ctx.unpack_sgd(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, gs, args)
+                self.ctx.unpack_sgd(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, go, args)
             self.launches += 1
 
     def close(self):
