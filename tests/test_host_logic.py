@@ -192,3 +192,51 @@ def test_short_division_is_correctly_rounded():
         q = (x * rcp).astype(np.float32)
         q2 = fma32(fma32(np.full_like(x, -dd), q, x), np.full_like(x, rcp), q)
         assert np.array_equal(q2, (x / dd).astype(np.float32)), d
+
+
+# ------------------------------------------------------------------ cross-GPU barrier protocol
+@pytest.mark.parametrize("world,seed", [(2, 0), (4, 1), (8, 2), (3, 3)])
+def test_flag_barrier_protocol_under_random_interleaving(world, seed):
+    """Model of csrc/p2p.cu peer_barrier + device-side generations: flag[dst][block][src] holds the
+    highest barrier generation block `block` of rank `src` has reached; block_gen[rank][block] is
+    advanced by two per launch.  Ranks run the SAME sequence of launches (grid sizes vary), kernels
+    of one rank run in stream order, everything else interleaves at random.  Must never deadlock,
+    and a block may only pass barrier g after every peer's same block reached g."""
+    rng = np.random.default_rng(seed)
+    grids = [int(g) for g in rng.integers(1, 6, 12)]                 # 12 launches, 1..5 blocks each
+    nblk = max(grids)
+    flag = np.zeros((world, nblk, world), np.int64)
+    gen = np.zeros((world, nblk), np.int64)
+    reached = np.zeros((world, nblk), np.int64)                      # ground truth: barriers entered so far
+    # per rank: index of the current launch and, per block of it, the phase 0..4
+    launch = [0] * world
+    phase = [[0] * grids[0] for _ in range(world)]
+    base = [[int(gen[r][b]) for b in range(grids[0])] for r in range(world)]
+    steps = 0
+    while any(l < len(grids) for l in launch):
+        steps += 1
+        assert steps < 200000, "barrier protocol deadlocked"
+        r = int(rng.integers(world))
+        if launch[r] >= len(grids):
+            continue
+        b = int(rng.integers(grids[launch[r]]))
+        ph, g0 = phase[r][b], base[r][b]
+        if ph in (0, 2):                                             # signal barrier g0+1 / g0+2 to every peer
+            g = g0 + 1 + ph // 2
+            reached[r][b] = g
+            flag[:, b, r] = g
+            phase[r][b] += 1
+        elif ph in (1, 3):                                           # wait for every peer's flag
+            g = g0 + 1 + ph // 2
+            if (flag[r, b, :] >= g).all():
+                assert (reached[:, b] >= g).all(), "passed a barrier a peer had not reached"
+                phase[r][b] += 1
+                if phase[r][b] == 4:
+                    gen[r][b] = g0 + 2
+        if all(p == 4 for p in phase[r]):                            # kernel done: next launch of this rank's stream
+            launch[r] += 1
+            if launch[r] < len(grids):
+                n = grids[launch[r]]
+                phase[r] = [0] * n
+                base[r] = [int(gen[r][bb]) for bb in range(n)]
+    assert (gen == gen[0]).all()                                     # every rank ends on the same generations
