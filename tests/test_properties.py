@@ -1,7 +1,7 @@
 """Property tests (hypothesis) of host-side logic and of the oracle.  CPU only."""
 import numpy as np
 import torch
-from hypothesis import given, settings, strategies as st
+from hypothesis import assume, given, settings, strategies as st
 from torch.utils.data.distributed import DistributedSampler
 
 import b200ddp
@@ -21,6 +21,7 @@ class _DS:
 @given(st.lists(st.integers(0, 50_000), min_size=0, max_size=40), st.sampled_from([2, 4]),
        st.integers(4_096, 400_000), st.integers(200_000, 2_000_000))
 def test_split_buckets_partitions_the_list(numels, esize, cap, staging):
+    assume(all(padded_numel(n) * esize <= staging for n in numels))     # a tensor beyond the staging area is an error
     out = split_buckets(numels, esize, cap, staging)
     # consecutive, complete, in order
     assert [lo for lo, _, _, _ in out] == [0] + [hi for _, hi, _, _ in out][:-1] if out else numels == []
