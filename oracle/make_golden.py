@@ -17,6 +17,8 @@ What is frozen:
   * ddp_grid_<variant>_ws<N>.npz - reference sync + torch SGD on a ragged tensor
     set with injected gradients (oracle/synth.py), several SGD flag sets.
   * sampler_*.npz - torch DistributedSampler (codes/task2/model.py:124) outputs.
+  * bf16_hook_ws{2,8}.npz - torch's bf16_compress_hook under DDP/gloo on injected gradients
+    (the semantics bf16 buckets are compared with; the reference itself is fp32 only).
 
 While generating, every oracle restatement (oracle/ref_ddp.py,
 oracle/sampler_oracle.py) is run on the same inputs and must agree bit for bit
@@ -148,6 +150,47 @@ def _grid_worker(rank, ws, port, tmp, variant, steps, kind):
     torch.distributed.destroy_process_group()
 
 
+def _bf16_hook_worker(rank, ws, port, tmp):
+    """torch's own bf16_compress_hook under DDP/gloo (the semantics `bf16 buckets` are held to):
+    a module whose gradients are exactly the injected tensors."""
+    from oracle import ref_ddp, synth
+    from torch.distributed.algorithms.ddp_comm_hooks import default_hooks
+    from torch.nn.parallel import DistributedDataParallel as DDP
+    torch.set_num_threads(1)
+    t4 = _load("ref_t4_dist_utils", f"{REF}/task4/dist_utils.py")
+    t4.dist_init(ws, rank, "127.0.0.1", str(port))
+
+    class Inject(torch.nn.Module):
+        def __init__(self):
+            super().__init__()
+            self.ps = torch.nn.ParameterList([torch.nn.Parameter(torch.zeros(n)) for n in synth.RAGGED_NUMELS])
+
+        def forward(self, xs):
+            return sum((p * x).sum() for p, x in zip(self.ps, xs))      # d/dp = x
+
+    model = DDP(Inject())
+    model.register_comm_hook(None, default_hooks.bf16_compress_hook)
+    xs = [torch.from_numpy(synth.dense_grad(n, rank, 0, t)) for t, n in enumerate(synth.RAGGED_NUMELS)]
+    model(xs).backward()
+    got = _flat([p.grad for p in model.module.ps])
+    mine = torch.cat([ref_ddp.bf16_wire_average(
+        [torch.from_numpy(synth.dense_grad(n, r, 0, t)) for r in range(ws)]) for t, n in enumerate(synth.RAGGED_NUMELS)]).numpy()
+    if ws <= 2:
+        assert np.array_equal(got, mine), "bf16_wire_average differs from torch's bf16_compress_hook"
+    else:       # gloo's bf16 summation order is not rank order
+        assert np.max(np.abs(got - mine)) <= 2e-2 * np.max(np.abs(got))
+    if rank == 0:
+        np.savez(os.path.join(tmp, "r0.npz"), avg=got)
+    torch.distributed.destroy_process_group()
+
+
+def make_bf16_hook(ws):
+    r0 = _spawn(_bf16_hook_worker, ws)["r0"]
+    r0["world"] = np.int64(ws)
+    np.savez_compressed(os.path.join(OUT, f"bf16_hook_ws{ws}.npz"), **r0)
+    print("bf16 hook ws", ws, "ok")
+
+
 def _spawn(fn, ws, *args):
     port = 29600 + (os.getpid() + _spawn.n) % 300
     _spawn.n += 1
@@ -249,6 +292,8 @@ def main():
         make_grid("A", ws)
     make_grid("A", 4, kind="dense")
     make_grid("A", 8, kind="dense")
+    make_bf16_hook(2)
+    make_bf16_hook(8)
 
 
 if __name__ == "__main__":
