@@ -30,7 +30,7 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 MODELS = {
-    # name: (ctor key for oracle.ref_ddp.build_model, per-rank batch, lr)
+    # name: (key for build_model below, per-rank batch, lr)
     "labnet": ("labnet", 32, 0.01),        # configs[0]: codes/task2/model.py:126,131
     "resnet18": ("resnet18", 128, 0.001),  # configs[1]: codes/task3/model.py:118
     "resnet50": ("resnet50", 256, 0.001),  # configs[2]

@@ -22,7 +22,6 @@ from ._lib import B200DDPError, SgdArgs, check, ptr_array
 _DTYPES = {"fp32": _lib.F32, "float32": _lib.F32, torch.float32: _lib.F32,
            "bf16": _lib.BF16, "bfloat16": _lib.BF16, torch.bfloat16: _lib.BF16,
            _lib.F32: _lib.F32, _lib.BF16: _lib.BF16}
-_TORCH_DTYPE = {_lib.F32: torch.float32, _lib.BF16: torch.bfloat16}
 _ESIZE = {_lib.F32: 4, _lib.BF16: 2}
 
 

@@ -154,40 +154,3 @@ def synthetic_batch(rank, step, batch, chw, classes):
         x = torch.rand((batch,) + tuple(chw), generator=g)
         y = torch.randint(0, classes, (batch,), generator=g)
     return x, y
-
-
-def build_model(name):
-    """Models of BASELINE.json's configs, constructed after manual_seed(0) so
-    that buffers agree across ranks."""
-    torch.manual_seed(0)
-    if name == "labnet":
-        return LabNet(1, 10), (1, 28, 28), 10
-    import torchvision
-    if name == "resnet18":
-        return torchvision.models.resnet18(num_classes=10), (3, 32, 32), 10
-    if name == "resnet50":
-        return torchvision.models.resnet50(), (3, 224, 224), 1000
-    raise ValueError(name)
-
-
-def train_steps(model, rank, steps, batch, chw, classes, lr=0.01, momentum=0.9,
-                sync=allreduce_average_gradients, record=None):
-    """The hot loop of codes/task2/model.py:49-63 on synthetic batches.
-    `record(step, local_grads, avg_grads)` is called after the sync."""
-    opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=momentum)
-    loss_fn = nn.CrossEntropyLoss()
-    model.train()
-    init_parameters(model)
-    losses = []
-    for s in range(steps):
-        x, y = synthetic_batch(rank, s, batch, chw, classes)
-        loss = loss_fn(model(x), y)
-        opt.zero_grad()
-        loss.backward()
-        local = [p.grad.detach().clone() for p in model.parameters()] if record else None
-        sync(model)
-        if record:
-            record(s, local, [p.grad.detach().clone() for p in model.parameters()])
-        opt.step()
-        losses.append(float(loss))
-    return opt, losses
