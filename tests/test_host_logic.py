@@ -240,3 +240,34 @@ def test_flag_barrier_protocol_under_random_interleaving(world, seed):
                 phase[r] = [0] * n
                 base[r] = [int(gen[r][bb]) for bb in range(n)]
     assert (gen == gen[0]).all()                                     # every rank ends on the same generations
+
+
+# ------------------------------------------------------------------ sampler classes: argument handling (no GPU needed)
+def test_sampler_constructors_match_torch_argument_handling():
+    from torch.utils.data.distributed import DistributedSampler as TorchDS
+
+    class DS:
+        def __init__(self, n):
+            self.n = n
+
+        def __len__(self):
+            return self.n
+
+    for n, world, drop_last in ((60000, 2, False), (10007, 4, True), (5, 8, False), (3, 8, True), (0, 2, False)):
+        mine = b200ddp.DistributedSampler(DS(n), num_replicas=world, rank=world - 1, drop_last=drop_last)
+        ref = TorchDS(DS(n), num_replicas=world, rank=world - 1, drop_last=drop_last)
+        assert (len(mine), mine.total_size, mine.epoch) == (len(ref), ref.total_size, 0)
+        mine.set_epoch(7)
+        assert mine.epoch == 7
+    for bad in (-1, 2):
+        with pytest.raises(ValueError, match="Invalid rank"):
+            b200ddp.DistributedSampler(DS(10), num_replicas=2, rank=bad)
+        with pytest.raises(ValueError, match="Invalid rank"):
+            TorchDS(DS(10), num_replicas=2, rank=bad)
+    with pytest.raises(RuntimeError):                       # no process group and no explicit replica count
+        b200ddp.DistributedSampler(DS(10))
+    # the reference skeleton's constructor (codes/task3/sampler.py:6-14): positional num_replicas, rank
+    s = b200ddp.MySampler(DS(1001), 4, 1, shuffle=True, seed=3)
+    assert (s.num_replicas, s.rank, s.shuffle, s.seed, s.epoch, len(s)) == (4, 1, True, 3, 0, 251)
+    with pytest.raises(ValueError):
+        b200ddp.MySampler(DS(10), 2, 0, mode="bogus")
