@@ -79,7 +79,9 @@ int b200ddp_adopt_symmetric(b200ddp_ctx *ctx, void *const *peer_ptrs, void *mc_p
 /* ---- plan: bucket layout of a list of T fp32 tensors ------------------------
  * Tensor t occupies bucket elements [offset[t], offset[t] + numel[t]); offsets
  * are aligned to 32 elements, the padding stays zero.  A plan is immutable and
- * owns the device-side chunk and pointer tables. */
+ * owns one device-side table (the chunk list).  Pointer arrays passed to the calls below are HOST
+ * arrays read at call time and copied into the kernel parameters: nothing is retained, a plan can
+ * be used from any stream, and a launch captured in a CUDA graph carries its pointers with it. */
 int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int bucket_dtype,
                         b200ddp_plan **out);
 int b200ddp_plan_destroy(b200ddp_plan *plan);
