@@ -6,7 +6,7 @@
 Per dataset length: device time of b200ddp_sampler_shard (CUDA events, median of
 10 after 3 warm-ups), device time + copy of the shard to the host (what
 DataLoader needs), torch.randperm and the whole torch DistributedSampler.__iter__
-on one host core, and the plain-C oracle.  The kernel is a latency chain (MT19937
+on one host core.  The kernel is a latency chain (MT19937
 recurrence, then ~log n reservation rounds), so microseconds per epoch is the
 figure of merit, not a bandwidth.
 """
@@ -29,7 +29,6 @@ def main():
     import torch
     from torch.utils.data.distributed import DistributedSampler
     import b200ddp
-    from oracle import sampler_oracle as so
 
     torch.cuda.set_device(0)
     ctx = b200ddp.Context(0, 1, 0, staging_bytes=1 << 20)
@@ -54,17 +53,15 @@ def main():
         ref = DistributedSampler(DS(), num_replicas=world, rank=0)
         ref.set_epoch(9)
         assert np.array_equal(host.numpy(), np.asarray(list(ref), dtype=np.int64))      # bit-exact while we are here
-        t_rp, t_it, t_c = [], [], []
+        t_rp, t_it = [], []
         for ep in range(5):
             g = torch.Generator().manual_seed(ep)
             t0 = time.perf_counter(); torch.randperm(n, generator=g); t_rp.append(time.perf_counter() - t0)
             ref.set_epoch(ep)
             t0 = time.perf_counter(); list(ref); t_it.append(time.perf_counter() - t0)
-            t0 = time.perf_counter(); so.c_distributed_sampler_indices(n, world, 0, 0, ep); t_c.append(time.perf_counter() - t0)
         med = statistics.median
         rows.append({"n": n, "world": world, "device_us": med(dev) * 1e6, "device_plus_d2h_us": med(e2e) * 1e6,
                      "torch_randperm_us": med(t_rp) * 1e6, "torch_sampler_iter_us": med(t_it) * 1e6,
-                     "c_oracle_us": med(t_c) * 1e6,
                      "speedup_vs_torch_randperm": med(t_rp) / med(dev),
                      "speedup_vs_torch_sampler_iter_incl_d2h": med(t_it) / med(e2e)})
         print(json.dumps(rows[-1]), flush=True)
