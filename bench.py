@@ -54,7 +54,9 @@ def parse():
     ap.add_argument("--step", default="graph", choices=["graph", "eager"],
                     help="graph: the loop body replayed from a CUDA graph; eager: the reference's Python loop")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--exact-warmup", action="store_true", help="do exactly --warmup steps (profiler runs)")
+    ap.add_argument("--settle", type=int, default=10,
+                    help="untimed set-up steps BEFORE the warm-up: cuDNN autotune, allocator growth, momentum "
+                         "buffers, CUDA-graph capture (0 for profiler runs)")
     ap.add_argument("--no-kernel-bench", action="store_true", help="skip the per-kernel roofline measurement")
     ap.add_argument("--cpu-budget-s", type=float, default=15.0)
     return ap.parse_args()
@@ -227,14 +229,32 @@ def _cpu_worker(rank, world, port, model_name, batch, lr, steps, warmup, threads
         torch.distributed.destroy_process_group()
 
 
+_LAUNCHER_ENV = ("RANK", "WORLD_SIZE", "LOCAL_RANK", "LOCAL_WORLD_SIZE", "GROUP_RANK", "GROUP_WORLD_SIZE",
+                 "ROLE_RANK", "ROLE_WORLD_SIZE", "ROLE_NAME", "MASTER_ADDR", "MASTER_PORT", "OMP_NUM_THREADS",
+                 "NCCL_ASYNC_ERROR_HANDLING", "TORCH_NCCL_ASYNC_ERROR_HANDLING")
+
+
+def scrub_launcher_env():
+    """The gloo workers below are a job of their own.  Launched under torch.distributed.run they
+    would inherit the agent's TORCHELASTIC_USE_AGENT_STORE (c10d then waits as a CLIENT of a store
+    nobody serves on the new port), its RANK / WORLD_SIZE / MASTER_* and OMP_NUM_THREADS=1."""
+    for k in list(os.environ):
+        if k.startswith("TORCHELASTIC_") or k in _LAUNCHER_ENV:
+            del os.environ[k]
+
+
 def run_cpu(world, model_name, batch, lr, steps, warmup):
     """Returns seconds for `steps` steps (max over ranks is rank 0's barrier-fenced time)."""
     import torch.multiprocessing as mp
+    scrub_launcher_env()
     cores = len(os.sched_getaffinity(0))
     threads = max(1, cores // world)
     ctx = mp.get_context("spawn")
     q = ctx.SimpleQueue()
-    port = 29800 + os.getpid() % 150
+    import socket
+    with socket.socket() as sk:                 # a port nobody holds right now
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
     procs = [ctx.Process(target=_cpu_worker, args=(r, world, port, model_name, batch, lr, steps, warmup, threads, q))
              for r in range(world)]
     for p in procs:
@@ -286,7 +306,8 @@ def reference_arm(args):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.model, batch, world, "cpu-gloo", None),
+            "config": workload_config(args.model, batch, world),
+            "arm": {"where": f"gloo x{world} on CPU", "threads_per_rank": threads, "sample_batch_per_rank": b},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads * world, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
@@ -294,15 +315,21 @@ def reference_arm(args):
     return 0
 
 
-def workload_config(model, batch, world, parallelism, extra):
-    cfg = {"workload": {"labnet": "task2 lab CNN on MNIST-shaped synthetic data (1x28x28)",
-                        "resnet18": "task3 DDP loop: ResNet-18 (10 classes) on CIFAR-10-shaped synthetic data (3x32x32)",
-                        "resnet50": "ResNet-50 on ImageNet-shaped synthetic data (3x224x224)"}[model],
-           "batch_per_rank": batch, "global_batch": batch * world, "optimizer": "SGD momentum 0.9",
-           "parallelism": f"{parallelism}{world}" if parallelism != "cpu-gloo" else f"gloo x{world} on CPU"}
-    if extra:
-        cfg.update(extra)
-    return cfg
+PARAMS = {"labnet": (51902, 8), "resnet18": (11181642, 62), "resnet50": (25557032, 161)}
+
+
+def workload_config(model, batch, world):
+    """The workload, spelled identically by both arms (what differs between them - where it runs,
+    wire dtype, algorithm - is in the line's `arm` object)."""
+    P, T = PARAMS[model]
+    return {"workload": {"labnet": "task2 lab CNN on MNIST-shaped synthetic data (1x28x28)",
+                         "resnet18": "task3 DDP loop: ResNet-18 (10 classes) on CIFAR-10-shaped synthetic data (3x32x32)",
+                         "resnet50": "ResNet-50 on ImageNet-shaped synthetic data (3x224x224)"}[model],
+            "batch_per_rank": batch, "global_batch": batch * world, "optimizer": "SGD momentum 0.9",
+            "parallelism": f"dp{world}", "params": P, "tensors": T,
+            "l2": "inputs larger than L2: the step's working set (params + momentum + grads = %.0f MB, plus "
+                  "activations) exceeds the 126 MB L2; kernel micro-benchmarks rotate 3 operand sets so every "
+                  "launch reads cold data" % (12 * P / 1e6)}
 
 
 # --------------------------------------------------------------------------- GPU arm
@@ -436,6 +463,7 @@ def gpu_arm(args):
     loss_fn = torch.nn.CrossEntropyLoss()
     params = list(model.parameters())
     P = sum(p.numel() for p in params)
+    assert (P, len(params)) == PARAMS[args.model], "model does not have the parameter list SURVEY.md section 8 names"
     host_batches = make_batches(rank, 8, batch, chw, classes, pin=True)
     dev_batches = [(x.to(dev), y.to(dev)) for x, y in host_batches]
     h2d = host_batches[0][0].numel() * 4 + host_batches[0][1].numel() * 8
@@ -489,9 +517,13 @@ def gpu_arm(args):
             dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    # host-bound loop: allocator, cuDNN heuristics and lazy module loads need ~10 steps to settle
-    warm = args.warmup if args.exact_warmup else max(args.warmup, 10)
-    for i in range(warm):
+    # set-up, not warm-up: cuDNN heuristics, allocator growth, lazy module loads, the momentum buffers'
+    # first-step rule and the CUDA-graph capture happen here, once, like model construction
+    settle = max(args.settle, gstep.eager_steps + 1) if gstep is not None else args.settle
+    for i in range(settle):
+        step(i, False)
+    fence()
+    for i in range(args.warmup):         # exactly --warmup steady-state steps
         step(i, False)
     fence()
     graphed = gstep is not None and gstep.graph is not None
@@ -576,12 +608,11 @@ def gpu_arm(args):
             dist.destroy_process_group()
         return 0
     line = {"metric": METRIC, "value": world * batch * args.steps / t_dev, "unit": UNIT, "n_gpus": world,
-            "steps": args.steps, "warmup": warm, "ms_per_step": t_dev / args.steps * 1e3,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(args.model, batch, world, "dp", {
-                "params": P, "tensors": len(params), "bucket_dtype": bucket_dtype, "mode": args.mode, "algo": args.algo,
-                "l2": "step working set (params+momentum+grads = %.0f MB plus activations) exceeds the 126 MB L2; "
-                      "kernel micro-benchmarks rotate 3 operand sets so every launch reads cold data" % (12 * P / 1e6)}),
+            "config": workload_config(args.model, batch, world),
+            "arm": {"where": f"{world} x B200, one process per GPU", "bucket_dtype": bucket_dtype, "mode": args.mode,
+                    "algo": args.algo, "settle_steps": settle},
             "e2e": {"value": world * batch * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "ms_per_step": t_e2e / args.steps * 1e3},
             "gpu_launches": launches, "clocks": clk, "roofline": roofline,

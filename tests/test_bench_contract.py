@@ -35,6 +35,31 @@ def test_reference_arm_prints_one_contract_line():
 
 def test_reference_arm_two_gloo_ranks_and_silent_other_ranks():
     d = json.loads(_run(None, "--gpus", "2").strip())
-    assert d["n_gpus"] == 2 and "gloo x2" in d["config"]["parallelism"] and d["value"] > 0
+    assert d["n_gpus"] == 2 and d["config"]["parallelism"] == "dp2" and "gloo x2" in d["arm"]["where"] and d["value"] > 0
     # under torchrun only rank 0 works and prints; the others exit 0 without a word
     assert _run({"RANK": "1", "WORLD_SIZE": "2", "LOCAL_RANK": "1"}, "--gpus", "2") == ""
+
+
+def test_reference_arm_survives_torch_distributed_run():
+    """Launched exactly as the driver launches it for N > 1.  The gloo workers must not inherit
+    the elastic agent's store settings (round 1: they did, and init_process_group never returned)."""
+    env = dict(os.environ)
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        env.pop(k, None)
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29731", os.path.join(ROOT, "bench.py"),
+                          "--impl", "reference", "--gpus", "2", "--model", "labnet", "--steps", "2", "--warmup", "1"],
+                         capture_output=True, text=True, env=env, timeout=120)
+    assert out.returncode == 0, out.stderr[-2000:]
+    lines = [ln for ln in out.stdout.splitlines() if ln.strip().startswith("{")]
+    assert len(lines) == 1, out.stdout
+    d = json.loads(lines[0])
+    assert d["impl"] == "reference" and d["n_gpus"] == 2 and d["steps"] == 2 and d["warmup"] == 1 and d["value"] > 0
+
+
+def test_both_arms_spell_the_workload_identically():
+    import bench
+    assert bench.workload_config("resnet18", 128, 4) == bench.workload_config("resnet18", 128, 4)
+    cfg = bench.workload_config("resnet18", 128, 4)
+    assert cfg["params"] == 11181642 and cfg["tensors"] == 62 and cfg["global_batch"] == 512
+    assert "model" not in cfg and "workload" in cfg
