@@ -7,10 +7,19 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import (POINTER, Structure, byref, c_char_p, c_double, c_float, c_int, c_int64,
+from ctypes import (POINTER, Structure, byref, c_char_p, c_double, c_float, c_int, c_int64, c_longlong,
                     c_size_t, c_uint64, c_void_p)
 
 F32, BF16 = 0, 1
+DIV_IEEE, DIV_RECIPROCAL = 0, 1
+(OPT_DIV_MODE, OPT_PDL, OPT_NVLS_MIN_BYTES, OPT_ONESHOT_MAX_BYTES, OPT_PEER_TIMEOUT_MS, OPT_P2P_BLOCKS,
+ OPT_NVLS_DEPTH, OPT_COPY_UNROLL, OPT_TRACE) = range(1, 10)
+OPTIONS = {"div_mode": OPT_DIV_MODE, "pdl": OPT_PDL, "nvls_min_bytes": OPT_NVLS_MIN_BYTES,
+           "oneshot_max_bytes": OPT_ONESHOT_MAX_BYTES, "peer_timeout_ms": OPT_PEER_TIMEOUT_MS,
+           "p2p_blocks": OPT_P2P_BLOCKS, "nvls_depth": OPT_NVLS_DEPTH, "copy_unroll": OPT_COPY_UNROLL,
+           "trace": OPT_TRACE}
+RULE_ADAM, RULE_GD = 1, 2
+MAX_BLOCKS_P2P = 1024
 ALGO_AUTO, ALGO_NCCL, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3, 4
 ALGO_NAMES = {"auto": ALGO_AUTO, "nccl": ALGO_NCCL, "oneshot": ALGO_ONESHOT, "twoshot": ALGO_TWOSHOT,
               "nvls": ALGO_NVLS}
@@ -33,6 +42,11 @@ class SgdArgs(Structure):
                 ("nesterov", c_int), ("maximize", c_int), ("first_step", c_int)]
 
 
+class OptArgs(Structure):
+    _fields_ = [("rule", c_int), ("lr", c_double), ("beta1", c_double), ("beta2", c_double), ("eps", c_double),
+                ("grad_divisor", c_double)]
+
+
 _PP = POINTER(c_void_p)
 
 _SIGNATURES = {
@@ -40,6 +54,9 @@ _SIGNATURES = {
     "b200ddp_version": (c_int, []),
     "b200ddp_create": (c_int, [c_int, c_int, c_int, c_size_t, POINTER(c_void_p)]),
     "b200ddp_destroy": (c_int, [c_void_p]),
+    "b200ddp_set_option": (c_int, [c_void_p, c_int, c_longlong]),
+    "b200ddp_get_option": (c_int, [c_void_p, c_int, POINTER(c_longlong)]),
+    "b200ddp_trace_read": (c_int, [c_void_p, POINTER(c_uint64), c_int]),
     "b200ddp_staging": (c_int, [c_void_p, POINTER(c_void_p), POINTER(c_size_t)]),
     "b200ddp_flags": (c_int, [c_void_p, POINTER(c_void_p)]),
     "b200ddp_peer_staging": (c_int, [c_void_p, c_int, POINTER(c_void_p)]),
@@ -59,6 +76,8 @@ _SIGNATURES = {
     "b200ddp_unpack": (c_int, [c_void_p, c_void_p, c_void_p, _PP, c_float, c_void_p]),
     "b200ddp_unpack_sgd": (c_int, [c_void_p, c_void_p, c_void_p, _PP, _PP, _PP, POINTER(SgdArgs), c_void_p]),
     "b200ddp_sgd_step": (c_int, [c_void_p, c_void_p, _PP, _PP, _PP, POINTER(SgdArgs), c_void_p]),
+    "b200ddp_unpack_opt": (c_int, [c_void_p, c_void_p, c_void_p, _PP, _PP, _PP, _PP, POINTER(OptArgs), c_void_p]),
+    "b200ddp_opt_step": (c_int, [c_void_p, c_void_p, _PP, _PP, _PP, _PP, POINTER(OptArgs), c_void_p]),
     "b200ddp_allreduce_sgd": (c_int, [c_void_p, c_void_p, c_size_t, _PP, _PP, _PP, POINTER(SgdArgs), c_void_p]),
     "b200ddp_emu_allreduce": (c_int, [_PP, c_int, c_size_t, c_int64, c_int, c_int, c_void_p, POINTER(c_size_t)]),
     "b200ddp_emu_allreduce_sgd": (c_int, [_PP, _PP, c_int, c_size_t, POINTER(_PP), POINTER(_PP), POINTER(_PP),
@@ -108,5 +127,5 @@ def ptr_array(ptrs) -> ctypes.Array:
     return (c_void_p * max(len(ptrs), 1))(*ptrs)
 
 
-__all__ = ["lib", "check", "last_error", "ptr_array", "SgdArgs", "B200DDPError", "byref",
+__all__ = ["lib", "check", "last_error", "ptr_array", "SgdArgs", "OptArgs", "B200DDPError", "byref",
            "F32", "BF16", "ALGO_AUTO", "ALGO_NCCL", "ALGO_ONESHOT", "ALGO_TWOSHOT", "ALGO_NAMES"]

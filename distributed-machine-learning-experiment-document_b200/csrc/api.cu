@@ -34,7 +34,8 @@ int check_ptrs(const b200ddp_plan *plan, PtrKind kind, const void *const *host_p
     return B200DDP_OK;
 }
 
-int sgd_scalars(const b200ddp_sgd_args *a, SgdScalars *o) {
+int sgd_scalars(const b200ddp_sgd_args *a, int div_mode, SgdScalars *o) {
+    memset(o, 0, sizeof(*o));
     B2_REQUIRE(a != nullptr, B200DDP_EINVAL, "sgd args is NULL");
     B2_REQUIRE(std::isfinite(a->lr) && std::isfinite(a->momentum) && std::isfinite(a->dampening) &&
                    std::isfinite(a->weight_decay) && std::isfinite(a->grad_divisor),
@@ -46,16 +47,84 @@ int sgd_scalars(const b200ddp_sgd_args *a, SgdScalars *o) {
     o->momentum = (float)a->momentum;
     o->one_minus_damp = (float)(1.0 - a->dampening);
     o->weight_decay = (float)a->weight_decay;
-    o->divisor = (float)a->grad_divisor;
-    o->div_rcp = 1.0f / o->divisor;
-    o->div_fast = fast_divisor(o->divisor) ? 1 : 0;
-    o->use_div = a->grad_divisor != 1.0;
+    o->dv = make_divisor((float)a->grad_divisor, div_mode);
+    o->rule = kRuleSgd;
     o->nesterov = a->nesterov != 0;
     o->maximize = a->maximize != 0;
     o->first_step = a->first_step != 0;
     o->has_momentum = a->momentum != 0.0;
     o->has_wd = a->weight_decay != 0.0;
     return B200DDP_OK;
+}
+
+int opt_scalars(const b200ddp_opt_args *a, int div_mode, SgdScalars *o) {
+    memset(o, 0, sizeof(*o));
+    B2_REQUIRE(a != nullptr, B200DDP_EINVAL, "optimizer args is NULL");
+    B2_REQUIRE(a->rule == B200DDP_RULE_ADAM || a->rule == B200DDP_RULE_GD, B200DDP_EINVAL, "bad update rule %d", a->rule);
+    B2_REQUIRE(std::isfinite(a->lr) && std::isfinite(a->grad_divisor) && a->grad_divisor != 0.0, B200DDP_EINVAL,
+               "bad lr or grad_divisor");
+    o->dv = make_divisor((float)a->grad_divisor, div_mode);
+    o->lr = (float)a->lr;
+    o->neg_lr = (float)(-a->lr);
+    if (a->rule == B200DDP_RULE_ADAM) {
+        B2_REQUIRE(std::isfinite(a->beta1) && std::isfinite(a->beta2) && std::isfinite(a->eps), B200DDP_EINVAL,
+                   "non-finite Adam hyper-parameter");
+        o->rule = kRuleAdam;
+        // Python evaluates (1 - beta) in double before the product with an fp32 tensor casts it
+        o->beta1 = (float)a->beta1;
+        o->one_minus_beta1 = (float)(1.0 - a->beta1);
+        o->beta2 = (float)a->beta2;
+        o->one_minus_beta2 = (float)(1.0 - a->beta2);
+        o->eps = (float)a->eps;
+        o->has_momentum = 1;
+    } else {
+        o->rule = kRuleGd;
+    }
+    return B200DDP_OK;
+}
+
+constexpr int kPdlDefault = 1;
+
+// value checks only; the caller holds whatever lock it needs
+static int set_option(b200ddp_ctx *ctx, int option, long long v) {
+    switch (option) {
+        case B200DDP_OPT_DIV_MODE:
+            B2_REQUIRE(v == B200DDP_DIV_IEEE || v == B200DDP_DIV_RECIPROCAL, B200DDP_EINVAL, "bad division mode %lld", v);
+            ctx->div_mode = (int)v;
+            return B200DDP_OK;
+        case B200DDP_OPT_PDL: ctx->pdl = v != 0; return B200DDP_OK;
+        case B200DDP_OPT_NVLS_MIN_BYTES: ctx->nvls_min_bytes = v < -2 ? -2 : v; return B200DDP_OK;
+        case B200DDP_OPT_ONESHOT_MAX_BYTES: ctx->oneshot_max_bytes = v < -2 ? -2 : v; return B200DDP_OK;
+        case B200DDP_OPT_PEER_TIMEOUT_MS: ctx->peer_timeout_ms = v < 0 ? 0 : v; return B200DDP_OK;
+        case B200DDP_OPT_P2P_BLOCKS:
+            B2_REQUIRE(v >= 0 && v <= kMaxBlocksP2P, B200DDP_EINVAL, "block cap %lld not in [0, %d]", v, kMaxBlocksP2P);
+            ctx->p2p_blocks = (int)v;
+            return B200DDP_OK;
+        case B200DDP_OPT_NVLS_DEPTH:
+            B2_REQUIRE(v == 0 || v == 1 || v == 2 || v == 4 || v == 8, B200DDP_EINVAL, "NVLS depth must be 1, 2, 4 or 8");
+            ctx->nvls_depth = (int)v;
+            return B200DDP_OK;
+        case B200DDP_OPT_COPY_UNROLL:
+            B2_REQUIRE(v == 2 || v == 4 || v == 8, B200DDP_EINVAL, "copy unroll must be 2, 4 or 8");
+            ctx->copy_unroll = (int)v;
+            return B200DDP_OK;
+        case B200DDP_OPT_TRACE: {
+            if (v != 0 && ctx->trace == nullptr) {
+                B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+                B2_CHECK_CUDA(cudaMalloc((void **)&ctx->trace, sizeof(unsigned long long) * 4 * kMaxBlocksP2P));
+                B2_CHECK_CUDA(cudaMemset(ctx->trace, 0, sizeof(unsigned long long) * 4 * kMaxBlocksP2P));
+            } else if (v == 0 && ctx->trace != nullptr) {
+                B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+                cudaDeviceSynchronize();
+                cudaFree(ctx->trace);
+                ctx->trace = nullptr;
+            }
+            return B200DDP_OK;
+        }
+        default:
+            set_error("unknown option %d", option);
+            return B200DDP_EINVAL;
+    }
 }
 
 static int check_plan(b200ddp_ctx *ctx, b200ddp_plan *plan) {
@@ -104,6 +173,20 @@ int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200dd
     int sms = 0;
     if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device) == cudaSuccess && sms > 0)
         ctx->sm_count = sms;
+    // environment defaults of the per-context options (b200ddp_set_option overrides)
+    auto env_ll = [](const char *name, long long dflt) {
+        const char *v = getenv(name);
+        return (v && *v) ? atoll(v) : dflt;
+    };
+    if (const char *m = getenv("B200DDP_DIV_MODE"))
+        ctx->div_mode = (m[0] == 'i' || m[0] == 'I' || m[0] == '0') ? B200DDP_DIV_IEEE : B200DDP_DIV_RECIPROCAL;
+    set_option(ctx, B200DDP_OPT_COPY_UNROLL, env_ll("B200DDP_COPY_UNROLL", ctx->copy_unroll));
+    set_option(ctx, B200DDP_OPT_PDL, env_ll("B200DDP_PDL", kPdlDefault));
+    set_option(ctx, B200DDP_OPT_NVLS_MIN_BYTES, env_ll("B200DDP_NVLS_MIN_BYTES", -2));
+    set_option(ctx, B200DDP_OPT_ONESHOT_MAX_BYTES, env_ll("B200DDP_ONESHOT_MAX_BYTES", -2));
+    set_option(ctx, B200DDP_OPT_PEER_TIMEOUT_MS, env_ll("B200DDP_PEER_TIMEOUT_MS", 0));
+    set_option(ctx, B200DDP_OPT_P2P_BLOCKS, env_ll("B200DDP_P2P_BLOCKS", 0));
+    set_option(ctx, B200DDP_OPT_NVLS_DEPTH, env_ll("B200DDP_NVLS_DEPTH", 0));
     const size_t flag_bytes = sizeof(uint32_t) * kMaxBlocksP2P * B200DDP_MAX_WORLD;
     cudaError_t e = cudaMalloc((void **)&ctx->staging, 2 * ctx->staging_bytes + 256);
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->flags, flag_bytes);
@@ -145,11 +228,45 @@ int b200ddp_destroy(b200ddp_ctx *ctx) {
         }
     }
     cudaFree(ctx->sampler_scratch);
+    cudaFree(ctx->trace);
     if (!ctx->staging_external) cudaFree(ctx->staging);
     cudaFree(ctx->flags);
     cudaFree(ctx->block_gen);
     cudaGetLastError();
     delete ctx;
+    return B200DDP_OK;
+}
+
+int b200ddp_set_option(b200ddp_ctx *ctx, int option, long long value) {
+    B2_REQUIRE(ctx != nullptr, B200DDP_EINVAL, "ctx is NULL");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return set_option(ctx, option, value);
+}
+
+int b200ddp_get_option(const b200ddp_ctx *ctx, int option, long long *value) {
+    B2_REQUIRE(ctx != nullptr && value != nullptr, B200DDP_EINVAL, "NULL argument");
+    switch (option) {
+        case B200DDP_OPT_DIV_MODE: *value = ctx->div_mode; break;
+        case B200DDP_OPT_PDL: *value = ctx->pdl ? 1 : 0; break;
+        case B200DDP_OPT_NVLS_MIN_BYTES: *value = ctx->nvls_min_bytes; break;
+        case B200DDP_OPT_ONESHOT_MAX_BYTES: *value = ctx->oneshot_max_bytes; break;
+        case B200DDP_OPT_PEER_TIMEOUT_MS: *value = ctx->peer_timeout_ms; break;
+        case B200DDP_OPT_P2P_BLOCKS: *value = ctx->p2p_blocks; break;
+        case B200DDP_OPT_NVLS_DEPTH: *value = ctx->nvls_depth; break;
+        case B200DDP_OPT_COPY_UNROLL: *value = ctx->copy_unroll; break;
+        case B200DDP_OPT_TRACE: *value = ctx->trace != nullptr; break;
+        default: set_error("unknown option %d", option); return B200DDP_EINVAL;
+    }
+    return B200DDP_OK;
+}
+
+int b200ddp_trace_read(b200ddp_ctx *ctx, uint64_t *out, int nblocks) {
+    B2_REQUIRE(ctx != nullptr && out != nullptr, B200DDP_EINVAL, "NULL argument");
+    B2_REQUIRE(ctx->trace != nullptr, B200DDP_ESTATE, "tracing is off (B200DDP_OPT_TRACE)");
+    B2_REQUIRE(nblocks >= 0 && nblocks <= kMaxBlocksP2P, B200DDP_EINVAL, "bad block count");
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    B2_CHECK_CUDA(cudaDeviceSynchronize());
+    B2_CHECK_CUDA(cudaMemcpy(out, ctx->trace, sizeof(uint64_t) * 4 * (size_t)nblocks, cudaMemcpyDeviceToHost));
     return B200DDP_OK;
 }
 
@@ -287,8 +404,10 @@ int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int buck
     p->device = ctx->device;
     p->T = T;
     p->dtype = bucket_dtype;
+    p->copy_unroll = ctx->copy_unroll;
+    const int64_t copy_chunk = (int64_t)kThreads * kVec * p->copy_unroll;
     int64_t off = 0;
-    Segment sg{0, 0, 0, 0};
+    Segment sg{0, 0, 0, 0, 0, 0};
     for (int t = 0; t < T; ++t) {
         if (numels[t] < 0) {
             set_error("tensor %d has negative numel", t);
@@ -298,30 +417,37 @@ int b200ddp_plan_create(b200ddp_ctx *ctx, int T, const int64_t *numels, int buck
         if (t - sg.t0 == kTabLarge) {            // table full: close the segment, open the next
             sg.t1 = t;
             sg.c1 = (int)p->chunks.size();
+            sg.k1 = (int)p->copy_chunks.size();
             p->segments.push_back(sg);
-            sg = Segment{t, t, sg.c1, sg.c1};
+            sg = Segment{t, t, sg.c1, sg.c1, sg.k1, sg.k1};
         }
         p->meta.push_back({numels[t], off});
         const int64_t nch = (numels[t] + kChunk - 1) / kChunk;
+        const int64_t ncp = (numels[t] + copy_chunk - 1) / copy_chunk;
         if (nch > INT32_MAX || p->chunks.size() + (size_t)nch > (size_t)INT32_MAX) {
             set_error("tensor list too large for one plan");
             delete p;
             return B200DDP_ETOOBIG;
         }
         for (int64_t c = 0; c < nch; ++c) p->chunks.push_back({t - sg.t0, (int)c});
+        for (int64_t c = 0; c < ncp; ++c) p->copy_chunks.push_back({t - sg.t0, (int)c});
         off += (numels[t] + kBucketAlign - 1) / kBucketAlign * kBucketAlign;
     }
     if (T > 0) {
         sg.t1 = T;
         sg.c1 = (int)p->chunks.size();
+        sg.k1 = (int)p->copy_chunks.size();
         p->segments.push_back(sg);
     }
     p->bucket_elems = off;
     cudaError_t e = cudaSuccess;
-    const size_t nC = p->chunks.empty() ? 1 : p->chunks.size();
-    e = cudaMalloc((void **)&p->d_chunks, sizeof(Chunk) * nC);
-    if (e == cudaSuccess && !p->chunks.empty())
-        e = cudaMemcpy(p->d_chunks, p->chunks.data(), sizeof(Chunk) * p->chunks.size(), cudaMemcpyHostToDevice);
+    const size_t nU = p->chunks.size(), nK = p->copy_chunks.size();
+    e = cudaMalloc((void **)&p->d_chunks, sizeof(Chunk) * (nU + nK + 1));
+    p->d_copy_chunks = p->d_chunks ? p->d_chunks + nU : nullptr;
+    if (e == cudaSuccess && nU)
+        e = cudaMemcpy(p->d_chunks, p->chunks.data(), sizeof(Chunk) * nU, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess && nK)
+        e = cudaMemcpy(p->d_copy_chunks, p->copy_chunks.data(), sizeof(Chunk) * nK, cudaMemcpyHostToDevice);
     if (e != cudaSuccess) {
         set_error("plan allocation failed: %s", cudaGetErrorString(e));
         b200ddp_plan_destroy(p);
@@ -360,7 +486,7 @@ int b200ddp_pack_scale(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
     if (int rc = check_ptrs(plan, kGradIn, grads)) return rc;
-    return launch_pack(plan, grads, bucket, scale, ctx->sm_count, s);
+    return launch_pack(plan, grads, bucket, scale, ctx->lc(), s);
 }
 
 int b200ddp_unpack(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, void *const *grads_out, float divisor,
@@ -372,11 +498,16 @@ int b200ddp_unpack(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, voi
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
     if (int rc = check_ptrs(plan, kGradOut, (const void *const *)grads_out)) return rc;
-    return launch_unpack(plan, bucket, (const void *const *)grads_out, divisor, ctx->sm_count, s);
+    return launch_unpack(plan, bucket, (const void *const *)grads_out, divisor, ctx->lc(), s);
 }
 
 static int update_tables(const b200ddp_plan *plan, const SgdScalars &hp, const void *const *grads,
-                         void *const *params, void *const *moms, void *const *grads_out, PtrArrays *pa) {
+                         void *const *params, void *const *moms, void *const *grads_out, PtrArrays *pa,
+                         void *const *vels = nullptr) {
+    if (hp.rule == kRuleAdam) {
+        if (int rc = check_ptrs(plan, kVel, (const void *const *)vels)) return rc;
+        pa->k[kVel] = (const void *const *)vels;
+    }
     if (int rc = check_ptrs(plan, kParam, (const void *const *)params)) return rc;
     pa->k[kParam] = (const void *const *)params;
     if (grads) {
@@ -401,20 +532,20 @@ int b200ddp_unpack_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket,
     B2_REQUIRE(bucket != nullptr || plan->bucket_elems == 0, B200DDP_EINVAL, "bucket is NULL");
     B2_REQUIRE(((uintptr_t)bucket & 15) == 0, B200DDP_EINVAL, "bucket must be 16-byte aligned");
     SgdScalars hp;
-    if (int rc = sgd_scalars(args, &hp)) return rc;
+    if (int rc = sgd_scalars(args, ctx->div_mode, &hp)) return rc;
     if (plan->bucket_elems == 0) return B200DDP_OK;
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
     PtrArrays pa;
     if (int rc = update_tables(plan, hp, nullptr, params, moms, grads_out, &pa)) return rc;
-    return launch_update(plan, bucket, pa, hp, ctx->sm_count, s);
+    return launch_update(plan, bucket, pa, hp, ctx->lc(), s);
 }
 
 int b200ddp_sgd_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads, void *const *params,
                      void *const *moms, const b200ddp_sgd_args *args, b200ddp_stream stream) {
     if (int rc = check_plan(ctx, plan)) return rc;
     SgdScalars hp;
-    if (int rc = sgd_scalars(args, &hp)) return rc;
+    if (int rc = sgd_scalars(args, ctx->div_mode, &hp)) return rc;
     if (plan->bucket_elems == 0) return B200DDP_OK;
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
@@ -422,7 +553,36 @@ int b200ddp_sgd_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *gr
     PtrArrays pa;
     if (int rc = update_tables(plan, hp, grads, params, moms, nullptr, &pa)) return rc;
     // direct mode: bucket == nullptr makes the kernel read the gradient tensors themselves
-    return launch_update(plan, nullptr, pa, hp, ctx->sm_count, s);
+    return launch_update(plan, nullptr, pa, hp, ctx->lc(), s);
+}
+
+int b200ddp_unpack_opt(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, void *const *params,
+                       void *const *state1, void *const *state2, void *const *grads_out,
+                       const b200ddp_opt_args *args, b200ddp_stream stream) {
+    if (int rc = check_plan(ctx, plan)) return rc;
+    B2_REQUIRE(bucket != nullptr || plan->bucket_elems == 0, B200DDP_EINVAL, "bucket is NULL");
+    B2_REQUIRE(((uintptr_t)bucket & 15) == 0, B200DDP_EINVAL, "bucket must be 16-byte aligned");
+    SgdScalars hp;
+    if (int rc = opt_scalars(args, ctx->div_mode, &hp)) return rc;
+    if (plan->bucket_elems == 0) return B200DDP_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    PtrArrays pa;
+    if (int rc = update_tables(plan, hp, nullptr, params, state1, grads_out, &pa, state2)) return rc;
+    return launch_update(plan, bucket, pa, hp, ctx->lc(), (cudaStream_t)stream);
+}
+
+int b200ddp_opt_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads, void *const *params,
+                     void *const *state1, void *const *state2, const b200ddp_opt_args *args,
+                     b200ddp_stream stream) {
+    if (int rc = check_plan(ctx, plan)) return rc;
+    SgdScalars hp;
+    if (int rc = opt_scalars(args, ctx->div_mode, &hp)) return rc;
+    if (plan->bucket_elems == 0) return B200DDP_OK;
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    B2_REQUIRE(grads != nullptr, B200DDP_EINVAL, "pointer table %d is NULL", (int)kGradIn);
+    PtrArrays pa;
+    if (int rc = update_tables(plan, hp, grads, params, state1, nullptr, &pa, state2)) return rc;
+    return launch_update(plan, nullptr, pa, hp, ctx->lc(), (cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------ K2
@@ -436,19 +596,21 @@ int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype) {
     // launch (fused one-shot + SGD) matters; two-shot moves 2 (N-1)/N x S and beats NCCL up to
     // ~128 MB (579 vs 419 GB/s busbw at 64 MB, 8 GPUs); above that NCCL's in-switch (NVLS)
     // reduction wins (727 vs 646 GB/s at 1 GiB).
-    const size_t oneshot_max = (size_t)(ctx->world <= 2 ? 1024 : ctx->world <= 4 ? 512 : 256) << 10;
-    if (bytes <= oneshot_max) return B200DDP_ALGO_ONESHOT;
+    const long long oneshot_max = ctx->oneshot_max_bytes != -2
+                                      ? ctx->oneshot_max_bytes
+                                      : (long long)(ctx->world <= 2 ? 1024 : ctx->world <= 4 ? 512 : 256) << 10;
+    if ((long long)bytes <= oneshot_max) return B200DDP_ALGO_ONESHOT;
     // In-switch reduction, when a multicast mapping was adopted.  Measured on 8 GPUs
     // (profiles/r01_sweep_n8_nvls_*.jsonl): level with two-shot up to 16 MB, then ahead - 574 vs
     // 551 GB/s at 64 MB, 768 vs 620 (NCCL 657) at 256 MB, 791 vs 641 (NCCL 720) at 1 GiB.  On 2
     // GPUs it loses (380 vs 626 GB/s at 256 MB): the switch has nothing to save there.
-    // B200DDP_NVLS_MIN_BYTES overrides the threshold (-1: never).
+    // B200DDP_OPT_NVLS_MIN_BYTES overrides the threshold (-1: never).
     if (ctx->mc_ptr) {
-        static const long long nvls_env = getenv("B200DDP_NVLS_MIN_BYTES") ? atoll(getenv("B200DDP_NVLS_MIN_BYTES")) : -2;
-        const long long nvls_min = nvls_env != -2 ? nvls_env : (ctx->world >= 8 ? (24ll << 20) : -1);
+        const long long nvls_min = ctx->nvls_min_bytes != -2 ? ctx->nvls_min_bytes : (ctx->world >= 8 ? (24ll << 20) : -1);
         if (nvls_min >= 0 && (long long)bytes >= nvls_min) return B200DDP_ALGO_NVLS;
     }
-    if (ctx->world > 4 && ctx->nccl_comm && bytes > ((size_t)128 << 20)) return B200DDP_ALGO_NCCL;
+    // NCCL only for fp32: ncclAllReduce on bf16 rounds at every step, the kernels here once
+    if (ctx->world > 4 && ctx->nccl_comm && dtype == B200DDP_F32 && bytes > ((size_t)128 << 20)) return B200DDP_ALGO_NCCL;
     return B200DDP_ALGO_TWOSHOT;
 }
 
@@ -484,14 +646,14 @@ int b200ddp_allreduce_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, size_t offset_by
     if (int rc = check_plan(ctx, plan)) return rc;
     if (int rc = in_staging(ctx, offset_bytes, plan->bucket_elems, plan->dtype)) return rc;
     SgdScalars hp;
-    if (int rc = sgd_scalars(args, &hp)) return rc;
+    if (int rc = sgd_scalars(args, ctx->div_mode, &hp)) return rc;
     if (plan->bucket_elems == 0) return B200DDP_OK;
     B2_REQUIRE(ctx->peers_ready, B200DDP_ESTATE, "peer memory not opened");
     std::lock_guard<std::mutex> lk(ctx->mu);
     cudaStream_t s = (cudaStream_t)stream;
     PtrArrays pa;
     if (int rc = update_tables(plan, hp, nullptr, params, moms, grads_out, &pa)) return rc;
-    if (ctx->world == 1) return launch_update(plan, ctx->staging + offset_bytes, pa, hp, ctx->sm_count, s);
+    if (ctx->world == 1) return launch_update(plan, ctx->staging + offset_bytes, pa, hp, ctx->lc(), s);
     return launch_oneshot_update(ctx, plan, offset_bytes, pa, hp, s);
 }
 
@@ -530,7 +692,7 @@ int b200ddp_emu_allreduce_sgd(b200ddp_ctx *const *ctxs, b200ddp_plan *const *pla
     if (int rc = check_emu(ctxs, n)) return rc;
     B2_REQUIRE(plans != nullptr && params != nullptr, B200DDP_EINVAL, "NULL argument");
     SgdScalars hp;
-    if (int rc = sgd_scalars(args, &hp)) return rc;
+    if (int rc = sgd_scalars(args, ctxs[0]->div_mode, &hp)) return rc;
     B2_REQUIRE(!hp.has_momentum || moms != nullptr, B200DDP_EINVAL, "momentum buffers missing");
     cudaStream_t s = (cudaStream_t)stream;
     B2_CHECK_CUDA(cudaSetDevice(ctxs[0]->device));

@@ -43,6 +43,16 @@ __device__ __forceinline__ void st_u2(void *p, const uint2 &v) {
     asm volatile("st.global.v2.u32 [%0], {%1,%2};" ::"l"(p), "r"(v.x), "r"(v.y) : "memory");
 }
 
+// ---- programmatic dependent launch -------------------------------------------------------
+// Every kernel of the library starts with these two.  Launched with the programmatic-stream-
+// serialization attribute (ctx->pdl), a kernel may be scheduled while its predecessor on the stream
+// drains: its blocks take the SM slots the predecessor's finished blocks leave and park in
+// griddepcontrol.wait until the predecessor has completed and flushed, which removes the launch gap
+// and the ramp between pack -> reduce -> update.  Without the attribute both are no-ops.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_prologue() { pdl_launch_dependents(); pdl_wait(); }
+
 // ---- bucket element access, 4 elements at a time -------------------------------
 __device__ __forceinline__ float4 bf16x4_to_f4(uint2 raw) {
     float4 r;
@@ -85,41 +95,69 @@ template <> struct Bucket<__nv_bfloat16> {
     static __device__ __forceinline__ void store1(__nv_bfloat16 *p, float v) { *p = __float2bfloat16_rn(v); }
 };
 
-// ---- x / d, correctly rounded ----------------------------------------------------------
-// `param.grad.data /= world_size` (codes/task2/dist_utils.py:42) is an IEEE division, and for
-// world sizes that are not powers of two it cannot be folded into an exact pre-scale.
+// ---- x / d ------------------------------------------------------------------------------
+// See DivKind in internal.h for which rule stands for which run of the reference.  The IEEE rule:
 // __fdiv_rn costs ~50 instructions per element and makes the kernel issue-bound (ncu, round 1:
 // unpack 27 us vs pack 14 us for the same bytes).  For a divisor known on the host, Markstein's
 // sequence gives the same correctly rounded quotient in three: q = RN(x * rcp), r = fma(-d, q, x)
 // (exact), q' = fma(r, rcp, q), valid while quotient and remainder stay in the normal range.
-__device__ __forceinline__ float div_rn(float x, float d, float rcp, int fast) {
-    if (fast) {
+__device__ __forceinline__ float apply_div(float x, const Divisor &dv) {
+    if (dv.kind == kDivNone) return x;
+    if (dv.kind == kDivRcp) return __fmul_rn(x, dv.rcp);
+    if (dv.kind == kDivFast) {
         const float ax = fabsf(x);
         if (ax > 1e-30f && ax < 1e30f) {
-            const float q = __fmul_rn(x, rcp);
-            return __fmaf_rn(__fmaf_rn(-d, q, x), rcp, q);
+            const float q = __fmul_rn(x, dv.rcp);
+            return __fmaf_rn(__fmaf_rn(-dv.d, q, x), dv.rcp, q);
         }
         if (ax == 0.0f) return x;          // +-0 / d = +-0
     }
-    return __fdiv_rn(x, d);
+    return __fdiv_rn(x, dv.d);
 }
 
-// ---- momentum SGD on one element ------------------------------------------------
-// Rounding sequence of torch/optim/sgd.py:322-380 on fp32 tensors, where every
-// add_(x, alpha=a) / add(x, alpha=a) is a single fused multiply-add and mul_ is
-// a rounded multiply.  g_avg returns what p.grad holds after the reference's
-// sync (codes/task2/dist_utils.py:41-42): the averaged gradient, before the
-// optimizer's own weight-decay / maximize transforms (those are out of place).
-__device__ __forceinline__ void sgd_elem(float g, float &p, float &m, float &g_avg, const SgdScalars &hp) {
-    if (hp.use_div) g = div_rn(g, hp.divisor, hp.div_rcp, hp.div_fast);
+// ---- the update rule on one element --------------------------------------------------------
+// g_avg returns what p.grad holds after the reference's sync (codes/task2/dist_utils.py:41-42):
+// the averaged gradient, before the optimizer's own transforms (those are out of place).
+//
+// kRuleSgd: rounding sequence of torch/optim/sgd.py:322-380 on fp32 tensors, where every
+//   add_(x, alpha=a) / add(x, alpha=a) is a single fused multiply-add and mul_ is a rounded multiply.
+// kRuleGd:  codes/task1/pytorch/MyOptimizer.py:23  p = p - lr * g      (two roundings: product, difference)
+// kRuleAdam: codes/task1/pytorch/MyOptimizer.py:38-43 (no bias correction), every tensor op rounded on its own:
+//   m = b1 * m + (1 - b1) * g;  v = b2 * v + (1 - b2) * g**2;  p = p - (lr / (sqrt(v) + eps)) * m
+//   where `lr / tensor` is torch's Tensor.__rtruediv__: reciprocal(tensor) * lr.
+template <int RULE>
+__device__ __forceinline__ void opt_elem(float g, float &p, float &m, float &v, float &g_avg, const SgdScalars &hp) {
+    g = apply_div(g, hp.dv);
     g_avg = g;
-    if (hp.maximize) g = -g;
-    if (hp.has_wd) g = __fmaf_rn(hp.weight_decay, p, g);
-    if (hp.has_momentum) {
-        m = hp.first_step ? g : __fmaf_rn(hp.one_minus_damp, g, __fmul_rn(m, hp.momentum));
-        g = hp.nesterov ? __fmaf_rn(hp.momentum, m, g) : m;
+    if (RULE == kRuleGd) {
+        p = __fsub_rn(p, __fmul_rn(hp.lr, g));
+    } else if (RULE == kRuleAdam) {
+        m = __fadd_rn(__fmul_rn(hp.beta1, m), __fmul_rn(hp.one_minus_beta1, g));
+        v = __fadd_rn(__fmul_rn(hp.beta2, v), __fmul_rn(hp.one_minus_beta2, __fmul_rn(g, g)));
+        const float den = __fadd_rn(__fsqrt_rn(v), hp.eps);
+        p = __fsub_rn(p, __fmul_rn(__fmul_rn(__frcp_rn(den), hp.lr), m));
+    } else {
+        if (hp.maximize) g = -g;
+        if (hp.has_wd) g = __fmaf_rn(hp.weight_decay, p, g);
+        if (hp.has_momentum) {
+            m = hp.first_step ? g : __fmaf_rn(hp.one_minus_damp, g, __fmul_rn(m, hp.momentum));
+            g = hp.nesterov ? __fmaf_rn(hp.momentum, m, g) : m;
+        }
+        p = __fmaf_rn(hp.neg_lr, g, p);
     }
-    p = __fmaf_rn(hp.neg_lr, g, p);
+}
+template <int RULE>
+__device__ __forceinline__ void opt_elem4(const float4 &g, float4 &p, float4 &m, float4 &v, float4 &ga,
+                                          const SgdScalars &hp) {
+    opt_elem<RULE>(g.x, p.x, m.x, v.x, ga.x, hp);
+    opt_elem<RULE>(g.y, p.y, m.y, v.y, ga.y, hp);
+    opt_elem<RULE>(g.z, p.z, m.z, v.z, ga.z, hp);
+    opt_elem<RULE>(g.w, p.w, m.w, v.w, ga.w, hp);
+}
+// the momentum-SGD rule, for the fused one-shot kernel
+__device__ __forceinline__ void sgd_elem(float g, float &p, float &m, float &g_avg, const SgdScalars &hp) {
+    float v = 0.f;
+    opt_elem<kRuleSgd>(g, p, m, v, g_avg, hp);
 }
 __device__ __forceinline__ void sgd_elem4(const float4 &g, float4 &p, float4 &m, float4 &ga, const SgdScalars &hp) {
     sgd_elem(g.x, p.x, m.x, ga.x, hp);

@@ -24,6 +24,7 @@ namespace b200ddp {
 namespace {
 
 constexpr int kP2PThreads = 512;
+constexpr int kNvlsDepthDefault = 4;   // multimem loads in flight per thread (profiles/r02_sweep_n8_nvls_variants.jsonl)
 
 __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -55,11 +56,12 @@ __device__ __forceinline__ unsigned long long global_ns() {
     return t;
 }
 
-// A peer that never arrives (crashed rank, mismatched call sequence) must not hang the GPU for
-// good: after kPeerTimeoutNs the block traps, which fails the launch with an error the host sees.
-constexpr unsigned long long kPeerTimeoutNs = 60ull * 1000 * 1000 * 1000;
-
-__device__ __forceinline__ void peer_barrier(const PeerTable &pt, int rank, int world, int bid, uint32_t gen) {
+// By default a block waits for its peers for as long as it takes, as an NCCL collective does: a
+// legitimately slow rank (evaluation on rank 0, a data-loader stall, the lab's straggler experiment)
+// must not crash the others.  B200DDP_OPT_PEER_TIMEOUT_MS > 0 turns a wait longer than that into a
+// trap, which fails the launch with an error the host sees (hang detection for debugging).
+__device__ __forceinline__ void peer_barrier(const PeerTable &pt, int rank, int world, int bid, uint32_t gen,
+                                             unsigned long long timeout_ns) {
     __syncthreads();
     if ((int)threadIdx.x < world) {
         const int peer = threadIdx.x;
@@ -67,14 +69,21 @@ __device__ __forceinline__ void peer_barrier(const PeerTable &pt, int rank, int 
         const uint32_t *mine = pt.flags[rank] + bid * B200DDP_MAX_WORLD + peer;
         unsigned long long t0 = 0;
         for (unsigned int spins = 0; (int32_t)(ld_acquire_sys(mine) - gen) < 0; ++spins) {
-            if ((spins & 0xfffu) == 0xfffu) {          // look at the clock every 4096 polls
+            if (timeout_ns != 0 && (spins & 0xfffu) == 0xfffu) {          // look at the clock every 4096 polls
                 const unsigned long long now = global_ns();
                 if (t0 == 0) t0 = now;
-                else if (now - t0 > kPeerTimeoutNs) __trap();
+                else if (now - t0 > timeout_ns) __trap();
             }
         }
     }
     __syncthreads();
+}
+
+// Optional per-block time stamps (B200DDP_OPT_TRACE): entry, first barrier passed, data moved,
+// last barrier passed.  ncu cannot replay a kernel that waits for other GPUs, so this is how the
+// phases of the cross-GPU kernels are measured (tools/p2p_trace.py).
+__device__ __forceinline__ void trace_stamp(unsigned long long *trace, int bid, int slot) {
+    if (trace != nullptr && threadIdx.x == 0) trace[bid * 4 + slot] = global_ns();
 }
 
 // ---- 16-byte vector arithmetic in fp32 ---------------------------------------
@@ -129,72 +138,119 @@ struct P2PArgs {
     // and is advanced by the kernel itself: a launch replayed from a CUDA graph must not carry
     // a generation number frozen at capture time.  EMU fills all ranks, a real launch only its own.
     uint32_t *gen[B200DDP_MAX_WORLD];
+    unsigned long long timeout_ns;   // 0: wait for ever
+    unsigned long long *trace;       // nullable: 4 stamps per block
 };
 
+// Sum of vector i over all ranks, in rank order, in fp32.
 // N > 0: unrolled for that world size; N == 0: runtime loop over args.world.
+// V vectors per thread are in flight together: V x N independent 16-byte peer loads, all issued
+// before the first add, so that one NVLink round trip (~2 us) covers V x N x 16 bytes per thread.
+template <typename BT, int N, int V>
+__device__ __forceinline__ void reduce_vectors(const P2PArgs &a, int world, const int64_t (&idx)[V], int64_t hi,
+                                               uint4 (&out)[V]) {
+    if (N > 0) {
+        uint4 v[V][N > 0 ? N : 1];
+#pragma unroll
+        for (int u = 0; u < V; ++u)
+            if (idx[u] < hi) {
+#pragma unroll
+                for (int r = 0; r < N; ++r)
+                    v[u][r] = ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + idx[u]);
+            }
+#pragma unroll
+        for (int u = 0; u < V; ++u)
+            if (idx[u] < hi) {
+                float acc[Vec16<BT>::kAcc];
+                Vec16<BT>::set(acc, v[u][0]);
+#pragma unroll
+                for (int r = 1; r < N; ++r) Vec16<BT>::add(acc, v[u][r]);
+                out[u] = Vec16<BT>::pack(acc);
+            }
+    } else {
+#pragma unroll
+        for (int u = 0; u < V; ++u)
+            if (idx[u] < hi) {
+                float acc[Vec16<BT>::kAcc];
+                Vec16<BT>::set(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[0] + a.off_bytes) + idx[u]));
+                for (int r = 1; r < world; ++r)
+                    Vec16<BT>::add(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + idx[u]));
+                out[u] = Vec16<BT>::pack(acc);
+            }
+    }
+}
+
+// vectors in flight per thread, by world size: V x N loads of 16 bytes
+template <int N> struct P2PUnroll { static constexpr int kV = N == 2 ? 4 : N == 4 ? 4 : N == 8 ? 2 : 1; };
+
 template <typename BT, int N, bool EMU>
 __global__ void __launch_bounds__(kP2PThreads) oneshot_kernel(P2PArgs a) {
+    constexpr int V = P2PUnroll<N>::kV;
     const int rank = EMU ? (int)blockIdx.y : a.rank;
     const int world = N > 0 ? N : a.world;
     const int bid = blockIdx.x;
+    unsigned long long *trace = EMU ? nullptr : a.trace;
+    pdl_prologue();
+    trace_stamp(trace, bid, 0);
     const uint32_t gen = a.gen[rank][bid];
-    peer_barrier(a.pt, rank, world, bid, gen + 1);
+    peer_barrier(a.pt, rank, world, bid, gen + 1, a.timeout_ns);
+    trace_stamp(trace, bid, 1);
     uint4 *dst = reinterpret_cast<uint4 *>(a.pt.staging[rank] + a.result_off);
     const int64_t stride = (int64_t)gridDim.x * kP2PThreads;
-    for (int64_t i = (int64_t)bid * kP2PThreads + threadIdx.x; i < a.nvec; i += stride) {
-        float acc[Vec16<BT>::kAcc];
-        if (N > 0) {
-            uint4 v[N > 0 ? N : 1];
+    for (int64_t i0 = (int64_t)bid * kP2PThreads + threadIdx.x; i0 < a.nvec; i0 += stride * V) {
+        int64_t idx[V];
+        uint4 out[V];
 #pragma unroll
-            for (int r = 0; r < N; ++r) v[r] = ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i);
-            Vec16<BT>::set(acc, v[0]);
+        for (int u = 0; u < V; ++u) idx[u] = i0 + u * stride;
+        reduce_vectors<BT, N, V>(a, world, idx, a.nvec, out);
 #pragma unroll
-            for (int r = 1; r < N; ++r) Vec16<BT>::add(acc, v[r]);
-        } else {
-            Vec16<BT>::set(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[0] + a.off_bytes) + i));
-            for (int r = 1; r < world; ++r)
-                Vec16<BT>::add(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i));
-        }
-        dst[i] = Vec16<BT>::pack(acc);
+        for (int u = 0; u < V; ++u)
+            if (idx[u] < a.nvec) dst[idx[u]] = out[u];
     }
-    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    trace_stamp(trace, bid, 2);
+    peer_barrier(a.pt, rank, world, bid, gen + 2, a.timeout_ns);
+    trace_stamp(trace, bid, 3);
     if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
 template <typename BT, int N, bool EMU>
 __global__ void __launch_bounds__(kP2PThreads) twoshot_kernel(P2PArgs a) {
+    constexpr int V = P2PUnroll<N>::kV;
     const int rank = EMU ? (int)blockIdx.y : a.rank;
     const int world = N > 0 ? N : a.world;
     const int bid = blockIdx.x;
+    unsigned long long *trace = EMU ? nullptr : a.trace;
+    pdl_prologue();
+    trace_stamp(trace, bid, 0);
     const uint32_t gen = a.gen[rank][bid];
-    peer_barrier(a.pt, rank, world, bid, gen + 1);
+    peer_barrier(a.pt, rank, world, bid, gen + 1, a.timeout_ns);
+    trace_stamp(trace, bid, 1);
     const int64_t per = (a.nvec + world - 1) / world;
     const int64_t lo = per * rank;
     const int64_t hi = lo + per < a.nvec ? lo + per : a.nvec;
     const int64_t stride = (int64_t)gridDim.x * kP2PThreads;
-    for (int64_t i = lo + (int64_t)bid * kP2PThreads + threadIdx.x; i < hi; i += stride) {
-        float acc[Vec16<BT>::kAcc];
-        if (N > 0) {
-            uint4 v[N > 0 ? N : 1];
+    for (int64_t i0 = lo + (int64_t)bid * kP2PThreads + threadIdx.x; i0 < hi; i0 += stride * V) {
+        int64_t idx[V];
+        uint4 out[V];
 #pragma unroll
-            for (int r = 0; r < N; ++r) v[r] = ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i);
-            Vec16<BT>::set(acc, v[0]);
+        for (int u = 0; u < V; ++u) idx[u] = i0 + u * stride;
+        reduce_vectors<BT, N, V>(a, world, idx, hi, out);
 #pragma unroll
-            for (int r = 1; r < N; ++r) Vec16<BT>::add(acc, v[r]);
-        } else {
-            Vec16<BT>::set(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[0] + a.off_bytes) + i));
-            for (int r = 1; r < world; ++r)
-                Vec16<BT>::add(acc, ld_peer_u4(reinterpret_cast<const uint4 *>(a.pt.staging[r] + a.off_bytes) + i));
-        }
-        const uint4 out = Vec16<BT>::pack(acc);
-        if (N > 0) {
+        for (int u = 0; u < V; ++u)
+            if (idx[u] < hi) {
+                if (N > 0) {
 #pragma unroll
-            for (int r = 0; r < N; ++r) st_peer_u4(reinterpret_cast<uint4 *>(a.pt.staging[r] + a.off_bytes) + i, out);
-        } else {
-            for (int r = 0; r < world; ++r) st_peer_u4(reinterpret_cast<uint4 *>(a.pt.staging[r] + a.off_bytes) + i, out);
-        }
+                    for (int r = 0; r < N; ++r)
+                        st_peer_u4(reinterpret_cast<uint4 *>(a.pt.staging[r] + a.off_bytes) + idx[u], out[u]);
+                } else {
+                    for (int r = 0; r < world; ++r)
+                        st_peer_u4(reinterpret_cast<uint4 *>(a.pt.staging[r] + a.off_bytes) + idx[u], out[u]);
+                }
+            }
     }
-    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    trace_stamp(trace, bid, 2);
+    peer_barrier(a.pt, rank, world, bid, gen + 2, a.timeout_ns);
+    trace_stamp(trace, bid, 3);
     if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
@@ -231,33 +287,48 @@ template <> struct Multimem<__nv_bfloat16> {
     }
 };
 
-constexpr int kNvlsUnroll = 4;
-
-template <typename BT>
+// The reduce phase loads the links outbound (every GPU feeds S to the switch) and the broadcast
+// phase loads them inbound (every GPU receives S); they only overlap if loads and stores are in
+// flight together.  Round 1's kernel issued 4 loads, then 4 stores, per thread, and at the bucket
+// sizes of the lab's models (5.6 MB per rank) that was ONE pass: all loads of all GPUs, then all
+// stores - the two directions used one after the other.  Here every thread keeps a ring of D
+// loads in flight and, slot by slot, stores a result and immediately issues the load that reuses
+// the slot, so from the second vector on both directions are busy.
+template <typename BT, int D>
 __global__ void __launch_bounds__(kP2PThreads) nvls_kernel(P2PArgs a, char *mc) {
     const int rank = a.rank, world = a.world, bid = blockIdx.x;
+    pdl_prologue();
+    trace_stamp(a.trace, bid, 0);
     const uint32_t gen = a.gen[rank][bid];
-    peer_barrier(a.pt, rank, world, bid, gen + 1);
+    peer_barrier(a.pt, rank, world, bid, gen + 1, a.timeout_ns);
+    trace_stamp(a.trace, bid, 1);
     const int64_t per = (a.nvec + world - 1) / world;
     const int64_t lo = per * rank;
     const int64_t hi = lo + per < a.nvec ? lo + per : a.nvec;
     const int64_t stride = (int64_t)gridDim.x * kP2PThreads;
     char *base = mc + a.off_bytes;
-    for (int64_t i0 = lo + (int64_t)bid * kP2PThreads + threadIdx.x; i0 < hi; i0 += stride * kNvlsUnroll) {
-        uint4 v[kNvlsUnroll];
+    const int64_t first = lo + (int64_t)bid * kP2PThreads + threadIdx.x;
+    uint4 v[D];
 #pragma unroll
-        for (int u = 0; u < kNvlsUnroll; ++u) {
-            const int64_t i = i0 + u * stride;
-            if (i < hi) v[u] = Multimem<BT>::ld_reduce(base + i * 16);
-        }
+    for (int u = 0; u < D; ++u) {
+        const int64_t i = first + u * stride;
+        if (i < hi) v[u] = Multimem<BT>::ld_reduce(base + i * 16);
+    }
+    for (int64_t i0 = first; i0 < hi; i0 += stride * D) {
 #pragma unroll
-        for (int u = 0; u < kNvlsUnroll; ++u) {
+        for (int u = 0; u < D; ++u) {
             const int64_t i = i0 + u * stride;
-            if (i < hi) Multimem<BT>::st(base + i * 16, v[u]);
+            if (i < hi) {
+                Multimem<BT>::st(base + i * 16, v[u]);
+                const int64_t nxt = i + stride * D;
+                if (nxt < hi) v[u] = Multimem<BT>::ld_reduce(base + nxt * 16);
+            }
         }
     }
     __threadfence_system();   // multimem stores are weak: order them before the barrier's release
-    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    trace_stamp(a.trace, bid, 2);
+    peer_barrier(a.pt, rank, world, bid, gen + 2, a.timeout_ns);
+    trace_stamp(a.trace, bid, 3);
     if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
@@ -279,8 +350,12 @@ __global__ void __launch_bounds__(kThreads) oneshot_update_kernel(P2PArgs a, con
     const Chunk *chunks = ts.chunks[EMU ? rank : 0];
     const int tid = threadIdx.x;
     const bool load_m = hp.has_momentum && !hp.first_step;
+    unsigned long long *trace = EMU ? nullptr : a.trace;
+    pdl_prologue();
+    trace_stamp(trace, bid, 0);
     const uint32_t gen = a.gen[rank][bid];
-    peer_barrier(a.pt, rank, world, bid, gen + 1);
+    peer_barrier(a.pt, rank, world, bid, gen + 1, a.timeout_ns);
+    trace_stamp(trace, bid, 1);
     for (int c = bid; c < nchunks; c += gridDim.x) {
         const Chunk ck = chunks[c];
         const int64_t e0 = (int64_t)ck.index * kChunk;
@@ -329,23 +404,27 @@ __global__ void __launch_bounds__(kThreads) oneshot_update_kernel(P2PArgs a, con
             if (WRITE_GRAD) go[i] = ga;
         }
     }
-    peer_barrier(a.pt, rank, world, bid, gen + 2);
+    trace_stamp(trace, bid, 2);
+    peer_barrier(a.pt, rank, world, bid, gen + 2, a.timeout_ns);
+    trace_stamp(trace, bid, 3);
     if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
-#define B2_LAUNCH_CHECK()                                                                              \
-    do {                                                                                               \
-        cudaError_t _e = cudaGetLastError();                                                           \
-        if (_e != cudaSuccess) {                                                                       \
-            set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__); \
-            return B200DDP_ECUDA;                                                                      \
-        }                                                                                              \
+#define B2_LAUNCH_RC(expr)                                                                              \
+    do {                                                                                                \
+        cudaError_t _e = (expr);                                                                        \
+        if (_e != cudaSuccess) {                                                                        \
+            set_error("kernel launch failed: %s (%s:%d)", cudaGetErrorString(_e), __FILE__, __LINE__);  \
+            cudaGetLastError();                                                                         \
+            return B200DDP_ECUDA;                                                                       \
+        }                                                                                               \
     } while (0)
 
-template <typename BT, int N, bool EMU> const void *pick_kernel(int algo) {
-    return algo == B200DDP_ALGO_ONESHOT ? (const void *)oneshot_kernel<BT, N, EMU> : (const void *)twoshot_kernel<BT, N, EMU>;
+typedef void (*P2PKernel)(P2PArgs);
+template <typename BT, int N, bool EMU> P2PKernel pick_kernel(int algo) {
+    return algo == B200DDP_ALGO_ONESHOT ? oneshot_kernel<BT, N, EMU> : twoshot_kernel<BT, N, EMU>;
 }
-template <typename BT, bool EMU> const void *pick_world(int algo, int world) {
+template <typename BT, bool EMU> P2PKernel pick_world(int algo, int world) {
     switch (world) {
         case 2: return pick_kernel<BT, 2, EMU>(algo);
         case 4: return pick_kernel<BT, 4, EMU>(algo);
@@ -353,10 +432,9 @@ template <typename BT, bool EMU> const void *pick_world(int algo, int world) {
         default: return pick_kernel<BT, 0, EMU>(algo);
     }
 }
-template <bool EMU> const void *pick(int dtype, int algo, int world) {
+template <bool EMU> P2PKernel pick(int dtype, int algo, int world) {
     return dtype == B200DDP_F32 ? pick_world<float, EMU>(algo, world) : pick_world<__nv_bfloat16, EMU>(algo, world);
 }
-
 P2PArgs make_args(const b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype) {
     P2PArgs a;
     a.pt = ctx->peers;
@@ -367,6 +445,8 @@ P2PArgs make_args(const b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype) 
     a.nvec = nelem * (dtype == B200DDP_BF16 ? 2 : 4) / 16;
     for (int r = 0; r < B200DDP_MAX_WORLD; ++r) a.gen[r] = nullptr;
     a.gen[ctx->rank] = ctx->block_gen;
+    a.timeout_ns = ctx->peer_timeout_ms > 0 ? (unsigned long long)ctx->peer_timeout_ms * 1000000ull : 0ull;
+    a.trace = ctx->trace;
     return a;
 }
 
@@ -381,7 +461,14 @@ void fill_update_tab(TensorTab<CAP, kNumPtrKinds> &tab, const b200ddp_plan *plan
         for (int i = 0; i < n; ++i) tab.ptr[k][i] = pa.k[k] ? const_cast<void *>(pa.k[k][sg.t0 + i]) : nullptr;
 }
 
-int update_grid(int nchunks) { return nchunks < 2 * kSmCount ? nchunks : 2 * kSmCount; }
+int block_cap(const b200ddp_ctx *ctx) {
+    int cap = ctx->p2p_blocks > 0 ? ctx->p2p_blocks : 2 * ctx->sm_count;
+    return cap < kMaxBlocksP2P ? cap : kMaxBlocksP2P;
+}
+int update_grid(const b200ddp_ctx *ctx, int nchunks) {
+    const int cap = block_cap(ctx);
+    return nchunks < cap ? nchunks : cap;
+}
 
 template <typename BT, bool WG, int CAP>
 int run_fused(b200ddp_ctx *ctx, const b200ddp_plan *plan, const Segment &sg, size_t off, const PtrArrays &pa,
@@ -391,21 +478,25 @@ int run_fused(b200ddp_ctx *ctx, const b200ddp_plan *plan, const Segment &sg, siz
     fill_update_tab(ts.t[0], plan, sg, pa);
     ts.chunks[0] = plan->d_chunks + sg.c0;
     const int n = sg.c1 - sg.c0;
-    cudaGetLastError();
-    oneshot_update_kernel<BT, WG, false, CAP><<<update_grid(n), kThreads, 0, s>>>(a, ts, n, hp);
-    B2_LAUNCH_CHECK();
+    B2_LAUNCH_RC(launch_ex(oneshot_update_kernel<BT, WG, false, CAP>, update_grid(ctx, n), kThreads, s, ctx->pdl, a, ts, n, hp));
     return B200DDP_OK;
+}
+
+int nvls_depth(const b200ddp_ctx *ctx) {
+    const int d = ctx->nvls_depth;
+    return (d == 1 || d == 2 || d == 4 || d == 8) ? d : kNvlsDepthDefault;
 }
 
 }  // namespace
 
-// Same on every rank: a pure function of the bucket and the world size.
-int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int sm_count) {
+// Same on every rank: a pure function of the bucket, the world size and settings that the caller
+// keeps equal on all ranks.
+int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int cap) {
     int64_t nvec = nelem * (dtype == B200DDP_BF16 ? 2 : 4) / 16;
-    if (algo == B200DDP_ALGO_TWOSHOT) nvec = (nvec + world - 1) / world;
-    // two vectors per thread per pass keeps enough loads in flight for the NVLink round trip
+    if (algo != B200DDP_ALGO_ONESHOT) nvec = (nvec + world - 1) / world;
+    // small buckets: two vectors per thread, so that few blocks (few flags) take part in the barrier
     int64_t g = (nvec + 2 * kP2PThreads - 1) / (2 * kP2PThreads);
-    const int cap = 2 * sm_count < kMaxBlocksP2P ? 2 * sm_count : kMaxBlocksP2P;
+    if (cap > kMaxBlocksP2P) cap = kMaxBlocksP2P;
     if (g < 1) g = 1;
     if (g > cap) g = cap;
     return (int)g;
@@ -413,20 +504,26 @@ int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int sm_count) {
 
 int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, int algo, cudaStream_t s) {
     P2PArgs a = make_args(ctx, off, nelem, dtype);
-    const int grid = p2p_grid_for(nelem, dtype, algo, ctx->world, kSmCount);
-    const void *k = pick<false>(dtype, algo, ctx->world);
-    void *params[] = {&a};
-    B2_CHECK_CUDA(cudaLaunchKernel(k, dim3(grid), dim3(kP2PThreads), params, 0, s));
+    const int grid = p2p_grid_for(nelem, dtype, algo, ctx->world, block_cap(ctx));
+    B2_LAUNCH_RC(launch_ex(pick<false>(dtype, algo, ctx->world), grid, kP2PThreads, s, ctx->pdl, a));
     return B200DDP_OK;
 }
 
 int launch_nvls_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, cudaStream_t s) {
     P2PArgs a = make_args(ctx, off, nelem, dtype);
-    const int grid = p2p_grid_for(nelem, dtype, B200DDP_ALGO_TWOSHOT, ctx->world, kSmCount);
-    cudaGetLastError();
-    if (dtype == B200DDP_F32) nvls_kernel<float><<<grid, kP2PThreads, 0, s>>>(a, ctx->mc_ptr);
-    else nvls_kernel<__nv_bfloat16><<<grid, kP2PThreads, 0, s>>>(a, ctx->mc_ptr);
-    B2_LAUNCH_CHECK();
+    const int grid = p2p_grid_for(nelem, dtype, B200DDP_ALGO_NVLS, ctx->world, block_cap(ctx));
+    cudaError_t e;
+#define B2_NVLS(D)                                                                                              \
+    (dtype == B200DDP_F32 ? launch_ex(nvls_kernel<float, D>, grid, kP2PThreads, s, ctx->pdl, a, ctx->mc_ptr)    \
+                          : launch_ex(nvls_kernel<__nv_bfloat16, D>, grid, kP2PThreads, s, ctx->pdl, a, ctx->mc_ptr))
+    switch (nvls_depth(ctx)) {
+        case 1: e = B2_NVLS(1); break;
+        case 2: e = B2_NVLS(2); break;
+        case 8: e = B2_NVLS(8); break;
+        default: e = B2_NVLS(4); break;
+    }
+#undef B2_NVLS
+    B2_LAUNCH_RC(e);
     return B200DDP_OK;
 }
 
@@ -434,10 +531,10 @@ int launch_p2p_allreduce_emu(b200ddp_ctx *const *ctxs, int n, size_t off, int64_
                              cudaStream_t s) {
     P2PArgs a = make_args(ctxs[0], off, nelem, dtype);
     for (int r = 0; r < n; ++r) a.gen[r] = ctxs[r]->block_gen;
-    const void *k = pick<true>(dtype, algo, n);
+    const void *k = (const void *)pick<true>(dtype, algo, n);
     int per_sm = 0;
     B2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kP2PThreads, 0));
-    int grid = p2p_grid_for(nelem, dtype, algo, n, kSmCount);
+    int grid = p2p_grid_for(nelem, dtype, algo, n, block_cap(ctxs[0]));
     const int fit = per_sm * ctxs[0]->sm_count / n;   // all ranks' blocks must be co-resident
     B2_REQUIRE(fit >= 1, B200DDP_ESTATE, "device cannot co-schedule %d emulated ranks", n);
     if (grid > fit) grid = fit;
@@ -470,7 +567,7 @@ int launch_oneshot_update_emu(b200ddp_ctx *const *ctxs, b200ddp_plan *const *pla
     if (plans[0]->segments.empty() || plans[0]->chunks.empty()) return B200DDP_OK;
     const Segment &sg = plans[0]->segments[0];
     P2PArgs a = make_args(ctxs[0], off, 0, plans[0]->dtype);
-    static TabSet<true, kTabSmall> ts;   // 12 KB: keep it off the stack
+    static TabSet<true, kTabSmall> ts;   // 14 KB: keep it off the stack
     for (int r = 0; r < B200DDP_MAX_WORLD; ++r) {
         const int q = r < n ? r : 0;
         a.gen[r] = ctxs[q]->block_gen;
@@ -488,7 +585,7 @@ int launch_oneshot_update_emu(b200ddp_ctx *const *ctxs, b200ddp_plan *const *pla
     int per_sm = 0;
     B2_CHECK_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k, kThreads, 0));
     int nchunks = sg.c1 - sg.c0;
-    int grid = update_grid(nchunks);
+    int grid = update_grid(ctxs[0], nchunks);
     const int fit = per_sm * ctxs[0]->sm_count / n;
     B2_REQUIRE(fit >= 1, B200DDP_ESTATE, "device cannot co-schedule %d emulated ranks", n);
     if (grid > fit) grid = fit;

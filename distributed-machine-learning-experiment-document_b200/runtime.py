@@ -17,7 +17,7 @@ import torch
 import torch.distributed as dist
 
 from . import _lib
-from ._lib import B200DDPError, SgdArgs, check, ptr_array
+from ._lib import B200DDPError, OptArgs, SgdArgs, check, ptr_array
 
 _DTYPES = {"fp32": _lib.F32, "float32": _lib.F32, torch.float32: _lib.F32,
            "bf16": _lib.BF16, "bfloat16": _lib.BF16, torch.bfloat16: _lib.BF16,
@@ -170,6 +170,28 @@ class Context:
         self.staging_ptr = tensor.data_ptr()
         self.has_multicast = bool(mc)
 
+    # ---- settings ------------------------------------------------------------
+    def set_option(self, name: str, value) -> "Context":
+        """Per-context settings (include/b200ddp.h, B200DDP_OPT_*): div_mode ("ieee" | "reciprocal"), pdl,
+        nvls_min_bytes, oneshot_max_bytes, peer_timeout_ms, p2p_blocks, nvls_depth, copy_unroll, trace.
+        Settings that shape a collective launch must be set to the same value on every rank."""
+        if name == "div_mode" and isinstance(value, str):
+            value = {"ieee": _lib.DIV_IEEE, "cpu": _lib.DIV_IEEE, "reciprocal": _lib.DIV_RECIPROCAL,
+                     "cuda": _lib.DIV_RECIPROCAL}[value]
+        check(_lib.lib().b200ddp_set_option(self.handle, _lib.OPTIONS[name], int(value)), f"set_option({name})")
+        return self
+
+    def get_option(self, name: str) -> int:
+        v = ctypes.c_longlong()
+        check(_lib.lib().b200ddp_get_option(self.handle, _lib.OPTIONS[name], byref(v)), f"get_option({name})")
+        return int(v.value)
+
+    def trace_read(self, nblocks: int):
+        """[(entry, barrier1, data, barrier2)] in ns for the first nblocks blocks of the last cross-GPU launch."""
+        buf = (ctypes.c_uint64 * (4 * nblocks))()
+        check(_lib.lib().b200ddp_trace_read(self.handle, buf, int(nblocks)), "trace_read")
+        return [tuple(buf[4 * i: 4 * i + 4]) for i in range(nblocks)]
+
     def link_local(self, peers: "list[Context]"):
         """Same-process peers (one process driving several contexts)."""
         st = ptr_array([c.staging_ptr for c in peers])
@@ -236,6 +258,22 @@ class Context:
             self.handle, plan.handle, ptr_array(grad_ptrs), ptr_array(param_ptrs),
             ptr_array(mom_ptrs) if mom_ptrs is not None else None, byref(args), _stream_handle(stream)), "sgd_step")
 
+    def unpack_opt(self, plan: Plan, bucket_ptr: int, param_ptrs, state1_ptrs, state2_ptrs, grad_out_ptrs,
+                   args: OptArgs, stream=None):
+        check(_lib.lib().b200ddp_unpack_opt(
+            self.handle, plan.handle, c_void_p(bucket_ptr), ptr_array(param_ptrs),
+            ptr_array(state1_ptrs) if state1_ptrs is not None else None,
+            ptr_array(state2_ptrs) if state2_ptrs is not None else None,
+            ptr_array(grad_out_ptrs) if grad_out_ptrs is not None else None,
+            byref(args), _stream_handle(stream)), "unpack_opt")
+
+    def opt_step(self, plan: Plan, grad_ptrs, param_ptrs, state1_ptrs, state2_ptrs, args: OptArgs, stream=None):
+        check(_lib.lib().b200ddp_opt_step(
+            self.handle, plan.handle, ptr_array(grad_ptrs), ptr_array(param_ptrs),
+            ptr_array(state1_ptrs) if state1_ptrs is not None else None,
+            ptr_array(state2_ptrs) if state2_ptrs is not None else None,
+            byref(args), _stream_handle(stream)), "opt_step")
+
     def allreduce_sgd(self, plan: Plan, offset_bytes: int, param_ptrs, mom_ptrs, grad_out_ptrs, args: SgdArgs,
                       stream=None):
         check(_lib.lib().b200ddp_allreduce_sgd(
@@ -289,6 +327,12 @@ def sgd_args(lr, momentum=0.0, dampening=0.0, weight_decay=0.0, nesterov=False, 
              first_step=False, grad_divisor=1.0) -> SgdArgs:
     return SgdArgs(float(lr), float(momentum), float(dampening), float(weight_decay), float(grad_divisor),
                    int(bool(nesterov)), int(bool(maximize)), int(bool(first_step)))
+
+
+def opt_args(rule, lr, beta1=0.9, beta2=0.999, eps=1e-8, grad_divisor=1.0) -> OptArgs:
+    """rule: "adam" | "gd" - the lab's own optimizers (codes/task1/pytorch/MyOptimizer.py:18-43)."""
+    code = {"adam": _lib.RULE_ADAM, "gd": _lib.RULE_GD}[rule]
+    return OptArgs(code, float(lr), float(beta1), float(beta2), float(eps), float(grad_divisor))
 
 
 # ---- per-process default context ---------------------------------------------------

@@ -32,6 +32,24 @@ enum { B200DDP_ALGO_AUTO = 0, B200DDP_ALGO_NCCL = 1,
 enum { B200DDP_OK = 0, B200DDP_EINVAL = -1, B200DDP_ECUDA = -2, B200DDP_ENCCL = -3,
        B200DDP_ESTATE = -4, B200DDP_ETOOBIG = -5 };
 
+/* how `param.grad.data /= world_size` (codes/task2/dist_utils.py:42) is rounded when world_size is not a
+ * power of two (for 2, 4, 8 both give the same bits):
+ *   RECIPROCAL  x * (float)(1/N): torch on CUDA - the reference's scripts run with backend "nccl" on .cuda()
+ *               tensors (codes/task2/dist_utils.py:12, codes/task2/model.py:128), where ATen divides by a
+ *               host scalar by multiplying with its reciprocal.  Default.
+ *   IEEE        the correctly rounded quotient: torch on the CPU (the gloo run). */
+enum { B200DDP_DIV_IEEE = 0, B200DDP_DIV_RECIPROCAL = 1 };
+/* b200ddp_set_option keys */
+enum { B200DDP_OPT_DIV_MODE = 1,          /* B200DDP_DIV_*                                                   */
+       B200DDP_OPT_PDL = 2,               /* 1: launch kernels with programmatic dependent launch            */
+       B200DDP_OPT_NVLS_MIN_BYTES = 3,    /* in-switch all-reduce from this size; -1 never; -2 built-in rule */
+       B200DDP_OPT_ONESHOT_MAX_BYTES = 4, /* one-shot all-reduce up to this size; -2 built-in rule           */
+       B200DDP_OPT_PEER_TIMEOUT_MS = 5,   /* cross-GPU barrier gives up (traps) after this long; 0: never     */
+       B200DDP_OPT_P2P_BLOCKS = 6,        /* grid cap of the P2P / NVLS kernels; 0: built-in (2 per SM)       */
+       B200DDP_OPT_NVLS_DEPTH = 7,        /* multimem loads in flight per thread (1, 2, 4, 8); 0: built-in    */
+       B200DDP_OPT_COPY_UNROLL = 8,       /* 128-bit accesses per thread in pack / unpack (2, 4, 8); new plans */
+       B200DDP_OPT_TRACE = 9 };           /* 1: the cross-GPU kernels stamp their phases (b200ddp_trace_read)   */
+
 #define B200DDP_MAX_WORLD 8
 #define B200DDP_IPC_BYTES 128   /* staging handle (64 B) + flag handle (64 B) */
 #define B200DDP_NCCL_UID_BYTES 128
@@ -49,6 +67,16 @@ int b200ddp_version(void);
  */
 int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200ddp_ctx **out);
 int b200ddp_destroy(b200ddp_ctx *ctx);
+/* Per-context settings (B200DDP_OPT_*); each has an environment default read at b200ddp_create
+ * (B200DDP_DIV_MODE=ieee|reciprocal, B200DDP_PDL, B200DDP_NVLS_MIN_BYTES, B200DDP_ONESHOT_MAX_BYTES,
+ * B200DDP_PEER_TIMEOUT_MS, B200DDP_P2P_BLOCKS, B200DDP_NVLS_DEPTH, B200DDP_COPY_UNROLL).  Settings that
+ * change the shape of a collective launch (grid, algorithm thresholds) must be equal on all ranks. */
+int b200ddp_set_option(b200ddp_ctx *ctx, int option, long long value);
+int b200ddp_get_option(const b200ddp_ctx *ctx, int option, long long *value);
+/* With B200DDP_OPT_TRACE on: 4 x nblocks nanosecond stamps (%globaltimer) of the LAST cross-GPU launch,
+ * per block: entry, first barrier passed, data phase done, last barrier passed.  Synchronises the device.
+ * (ncu cannot replay a kernel that waits for other GPUs; this is the library's own phase profile.) */
+int b200ddp_trace_read(b200ddp_ctx *ctx, uint64_t *out /* 4 x nblocks */, int nblocks);
 int b200ddp_staging(b200ddp_ctx *ctx, void **ptr, size_t *bytes);
 int b200ddp_flags(b200ddp_ctx *ctx, void **ptr);
 /* this process's mapping of rank `peer`'s staging area (after the peers are opened); used by
@@ -103,7 +131,9 @@ int b200ddp_pack_scale(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *
  * reduce in place; one-shot writes its result into the second half.
  * *result_offset_bytes receives where the sums are, relative to the staging
  * base.  Every rank must make the same calls in the same order.  world == 1
- * is a no-op.  bf16 buckets are summed in fp32 and rounded once. */
+ * is a no-op.  bf16 buckets are summed in fp32 and rounded once by the one-shot, two-shot and NVLS
+ * kernels; B200DDP_ALGO_NCCL is ncclAllReduce on ncclBfloat16, which rounds at every reduction step,
+ * so AUTO never picks NCCL for a bf16 bucket. */
 int b200ddp_allreduce(b200ddp_ctx *ctx, size_t offset_bytes, int64_t nelem, int dtype, int algo,
                       b200ddp_stream stream, size_t *result_offset_bytes);
 /* which algorithm AUTO resolves to for this size (host-only, no device work) */
@@ -112,7 +142,7 @@ int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype);
 /* ---- unpack (bucket -> p.grad) ----------------------------------------------
  * Replaces the write side of the in-place all_reduce and `param.grad.data /=
  * world_size`, codes/task2/dist_utils.py:41-42: grads_out[t][i] =
- * float(bucket[offset[t] + i]) / divisor (IEEE division; divisor 1 skips it). */
+ * float(bucket[offset[t] + i]) / divisor (rounded as B200DDP_OPT_DIV_MODE says; divisor 1 skips it). */
 int b200ddp_unpack(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket,
                    void *const *grads_out, float divisor, b200ddp_stream stream);
 
@@ -135,6 +165,25 @@ int b200ddp_unpack_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket,
 /* gradients come from T separate tensors (world == 1, or after b200ddp_unpack) */
 int b200ddp_sgd_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads,
                      void *const *params, void *const *moms, const b200ddp_sgd_args *args,
+                     b200ddp_stream stream);
+
+/* ---- K3 with the lab's own optimizers ----------------------------------------
+ * Replaces GdOptimizer.step / AdamOptimizer.step, codes/task1/pytorch/MyOptimizer.py:18-43, fused with the
+ * unpack like b200ddp_unpack_sgd.  GD: p = p - lr * g.  ADAM (no bias correction, as the lab writes it):
+ * m = b1 m + (1 - b1) g;  v = b2 v + (1 - b2) g^2;  p = p - (lr / (sqrt(v) + eps)) m, every tensor
+ * operation rounded on its own as torch evaluates that expression.  m and v start as zeros (:32-33) and are
+ * the caller's tensors (state1, state2; unused and nullable for GD). */
+enum { B200DDP_RULE_ADAM = 1, B200DDP_RULE_GD = 2 };
+typedef struct {
+    int rule;                      /* B200DDP_RULE_*                                  */
+    double lr, beta1, beta2, eps;  /* betas and eps unused for GD                     */
+    double grad_divisor;           /* g <- g / grad_divisor first; 1 = skip           */
+} b200ddp_opt_args;
+int b200ddp_unpack_opt(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *bucket, void *const *params,
+                       void *const *state1, void *const *state2, void *const *grads_out,
+                       const b200ddp_opt_args *args, b200ddp_stream stream);
+int b200ddp_opt_step(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *grads, void *const *params,
+                     void *const *state1, void *const *state2, const b200ddp_opt_args *args,
                      b200ddp_stream stream);
 
 /* ---- K2+K3 fused: one-shot peer reduction feeding the update directly -------

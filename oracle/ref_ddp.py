@@ -73,12 +73,31 @@ def average_gradients(model):
 # Exact for N <= 2 (fp32 addition is commutative, there is one addition);
 # for N > 2 gloo's order may differ, so callers use the stated tolerance.
 # --------------------------------------------------------------------------
-def average_over_ranks(per_rank: list[torch.Tensor]) -> torch.Tensor:
+def divide_by_world(x, n, rule="cpu"):
+    """`param.grad.data /= world_size` (codes/task2/dist_utils.py:42) on a float32 numpy array.
+    rule "cpu": the correctly rounded quotient - ATen's CPU kernel, i.e. the gloo run of the lab.
+    rule "cuda": x * fp32(1/n) - ATen's CUDA kernel multiplies by the reciprocal when the divisor
+    is a host scalar (div_true_kernel_cuda), and the reference's scripts run there (backend "nccl",
+    codes/task2/dist_utils.py:12).  Pinned on the GPU box against torch itself
+    (tests/test_gpu_kernels.py::test_reciprocal_division_is_what_torch_cuda_computes).
+    Both rules agree bit for bit when n is a power of two."""
+    x = np.asarray(x, np.float32)
+    if rule == "cuda":
+        return (x * (np.float32(1.0) / np.float32(n))).astype(np.float32)
+    if rule != "cpu":
+        raise ValueError(rule)
+    with np.errstate(all="ignore"):
+        return (x / np.float32(n)).astype(np.float32)
+
+
+def average_over_ranks(per_rank: list[torch.Tensor], rule="cpu") -> torch.Tensor:
     acc = per_rank[0].clone()
     for t in per_rank[1:]:
         acc += t
-    acc /= len(per_rank)
-    return acc
+    if rule == "cpu":
+        acc /= len(per_rank)
+        return acc
+    return torch.from_numpy(divide_by_world(acc.numpy(), len(per_rank), rule))
 
 
 def bf16_wire_average(per_rank: list[torch.Tensor]) -> torch.Tensor:

@@ -68,8 +68,13 @@ def test_pack_misaligned_tensors_take_the_scalar_path(ctx1):
 
 
 # ----------------------------------------------------------------------------- unpack
+RULES = {"ieee": "cpu", "reciprocal": "cuda"}      # library option -> oracle rule
+
+
+@pytest.mark.parametrize("rule", sorted(RULES))
 @pytest.mark.parametrize("divisor", [1.0, 2.0, 3.0, 7.0])
-def test_pack_unpack_divides_like_the_reference(ctx1, divisor):
+def test_pack_unpack_divides_like_the_reference(ctx1, divisor, rule):
+    ctx1.set_option("div_mode", rule)
     plan = ctx1.plan(RAGGED)
     g = _grads(RAGGED)
     gd = to_dev(g)
@@ -77,7 +82,26 @@ def test_pack_unpack_divides_like_the_reference(ctx1, divisor):
     ctx1.pack_scale(plan, ptrs(gd), ctx1.bucket_ptr(0), 1.0)
     ctx1.unpack(plan, ctx1.bucket_ptr(0), ptrs(out), divisor)
     for got, ref in zip(host(out), g):
-        assert np.array_equal(got, ref / np.float32(divisor))      # `param.grad.data /= world_size`
+        assert np.array_equal(got, ref_ddp.divide_by_world(ref, divisor, RULES[rule]))   # `param.grad.data /= world_size`
+
+
+@pytest.mark.parametrize("n", [3, 5, 6, 7, 2, 8])
+def test_reciprocal_division_is_what_torch_cuda_computes(ctx1, n):
+    """Pins the "cuda" rule of the oracle and the library's default on the real thing: torch on this
+    GPU dividing a tensor in place by a Python int, as codes/task2/dist_utils.py:42 does."""
+    rng = np.random.default_rng(n)
+    x = (rng.standard_normal(200_003) * 10.0 ** rng.integers(-30, 30, 200_003)).astype(np.float32)
+    t = torch.from_numpy(x).to(dev())
+    ref = t.clone()
+    ref /= n
+    ref = ref.cpu().numpy()
+    assert np.array_equal(ref.view(np.uint32), ref_ddp.divide_by_world(x, n, "cuda").view(np.uint32))
+    assert ctx1.get_option("div_mode") == b200ddp._lib.DIV_RECIPROCAL          # the default
+    plan = ctx1.plan((x.size,))
+    out = torch.empty_like(t)
+    ctx1.pack_scale(plan, [t.data_ptr()], ctx1.bucket_ptr(0), 1.0)
+    ctx1.unpack(plan, ctx1.bucket_ptr(0), [out.data_ptr()], float(n))
+    assert np.array_equal(out.cpu().numpy().view(np.uint32), ref.view(np.uint32))
 
 
 # ----------------------------------------------------------------------------- K3 update
@@ -124,9 +148,11 @@ def test_update_matches_torch_sgd(ctx1, variant, mode):
             assert np.array_equal(got, ref)
 
 
-def test_update_with_divisor_matches_sum_then_divide(ctx1):
+@pytest.mark.parametrize("rule", sorted(RULES))
+def test_update_with_divisor_matches_sum_then_divide(ctx1, rule):
     """Non-power-of-two worlds: the bucket holds the SUM and K3 divides, as
     codes/task2/dist_utils.py:42 does."""
+    ctx1.set_option("div_mode", rule)
     numels, hp = (1000, 4099), dict(lr=0.01, momentum=0.9)
     plan = ctx1.plan(numels)
     gsum = _grads(numels)
@@ -136,7 +162,7 @@ def test_update_with_divisor_matches_sum_then_divide(ctx1):
     ctx1.unpack_sgd(plan, ctx1.bucket_ptr(0), ptrs(p), ptrs(m), ptrs(gout),
                     b200ddp.sgd_args(first_step=True, grad_divisor=3.0, **hp))
     for t in range(len(numels)):
-        avg = gsum[t] / np.float32(3)
+        avg = ref_ddp.divide_by_world(gsum[t], 3, RULES[rule])
         pr, mr = ref_ddp.sgd_step_numpy(p0[t], avg, None, **hp)
         assert np.array_equal(host(gout)[t], avg) and np.array_equal(host(p)[t], pr) and np.array_equal(host(m)[t], mr)
 
@@ -157,10 +183,13 @@ def test_update_from_bf16_bucket(ctx1):
 
 
 # ----------------------------------------------------------------------------- golden: N ranks emulated on one GPU
-def _run_emulated(ws, numels, local_grads, p0, hp, steps, algo, dtype="fp32", fused=False):
+def _run_emulated(ws, numels, local_grads, p0, hp, steps, algo, dtype="fp32", fused=False, rule=None):
     """local_grads[s][r] -> list of per-tensor arrays.  Returns per-rank (p, m, avg) after `steps`."""
     w = EmuWorld(ws)
     try:
+        if rule is not None:
+            for c in w.ctxs:
+                c.set_option("div_mode", rule)
         plans = [c.plan(numels, dtype) for c in w.ctxs]
         P = [to_dev(p0) for _ in range(ws)]
         M = [[torch.full((n,), float("nan"), device=dev()) for n in numels] for _ in range(ws)]
@@ -264,18 +293,21 @@ def test_bf16_wire_within_stated_bounds(ws, algo):
         assert np.array_equal(avg, out[0][2])
 
 
-@pytest.mark.parametrize("ws", [3, 5])
-def test_odd_world_divides_after_the_sum(ws):
-    """Non-power-of-two worlds: sum, then true division - exactly the reference's order."""
+@pytest.mark.parametrize("rule", sorted(RULES))
+@pytest.mark.parametrize("algo", ["oneshot", "twoshot", "fused"])
+@pytest.mark.parametrize("ws", [3, 5, 6, 7])
+def test_odd_world_divides_after_the_sum(ws, algo, rule):
+    """Non-power-of-two worlds: sum in rank order, THEN divide - the reference's order - with the
+    division rounded as the chosen run of the reference rounds it; bit for bit on every rank."""
     numels = (1000, 4099)
     local = [[[synth.dense_grad(n, r, 0, t) for t, n in enumerate(numels)] for r in range(ws)]]
     p0 = [synth.init_param(n, t) for t, n in enumerate(numels)]
-    out = _run_emulated(ws, numels, local, p0, dict(lr=0.01), 1, "twoshot")
-    want = ref_ddp.average_over_ranks([torch.from_numpy(np.concatenate(local[0][r])) for r in range(ws)]).numpy()
+    out = _run_emulated(ws, numels, local, p0, dict(lr=0.01), 1, "oneshot" if algo == "fused" else algo,
+                        fused=(algo == "fused"), rule=rule)
+    want = ref_ddp.average_over_ranks([torch.from_numpy(np.concatenate(local[0][r])) for r in range(ws)],
+                                      RULES[rule]).numpy()
     for r in range(ws):
-        if ws == 3:
-            assert np.max(np.abs(out[r][2] - want)) <= 1e-6 * np.max(np.abs(want))
-        assert np.array_equal(out[r][2], out[0][2])
+        assert np.array_equal(out[r][2], want)
 
 
 # ----------------------------------------------------------------------------- full-size properties
@@ -345,6 +377,7 @@ def test_empty_plan_is_a_noop(ctx1):
 def test_division_edge_values_match_ieee(ctx1, divisor):
     """The short division sequence (small integer divisors) and its __fdiv_rn fallback (everything
     else: zeros, denormals, huge values, non-integer divisors) both give the IEEE quotient."""
+    ctx1.set_option("div_mode", "ieee")
     rng = np.random.default_rng(3)
     n = 70001
     x = (rng.standard_normal(n) * 10.0 ** rng.integers(-44, 38, n)).astype(np.float32)

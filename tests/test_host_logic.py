@@ -271,3 +271,19 @@ def test_sampler_constructors_match_torch_argument_handling():
     assert (s.num_replicas, s.rank, s.shuffle, s.seed, s.epoch, len(s)) == (4, 1, True, 3, 0, 251)
     with pytest.raises(ValueError):
         b200ddp.MySampler(DS(10), 2, 0, mode="bogus")
+
+
+@pytest.mark.parametrize("n", [2, 3, 4, 5, 6, 7, 8])
+def test_oracle_division_rules(n):
+    """The two roundings of `grad /= world_size`: identical for power-of-two worlds, at most one ulp
+    apart otherwise (and really different somewhere, which is why the rule is an option)."""
+    from oracle import ref_ddp
+    rng = np.random.default_rng(n)
+    x = (rng.standard_normal(100_000) * 10.0 ** rng.integers(-20, 20, 100_000)).astype(np.float32)
+    cpu, cuda = ref_ddp.divide_by_world(x, n, "cpu"), ref_ddp.divide_by_world(x, n, "cuda")
+    assert np.array_equal(cpu, (torch.from_numpy(x) / n).numpy())          # ATen's CPU kernel is the true quotient
+    if n & (n - 1) == 0:
+        assert np.array_equal(cpu, cuda)
+    else:
+        ulp = np.abs(cpu.view(np.int32).astype(np.int64) - cuda.view(np.int32).astype(np.int64))
+        assert ulp.max() == 1

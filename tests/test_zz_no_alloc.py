@@ -1,15 +1,18 @@
 """b200ddp_sampler_shard_static: the sampler shard for callers that must not
 allocate (their own pool owns the device memory, or they cannot take
 cudaMalloc's device-wide stall).  Called through the C ABI and compared with
-the regular entry point, which has already been checked against torch.
+the regular entry point, which has already been checked against torch, and
+directly with the committed torch golden vector and the C restatement.
 
 Integer output, so the comparison is exact - the tolerance every sampler test
 in this suite uses.  This file sorts last on purpose: a `-x` run reaches it only
 after everything else has run.
 """
 import ctypes
+import os
 from ctypes import c_void_p
 
+import numpy as np
 import pytest
 import torch
 
@@ -57,6 +60,24 @@ def test_static_sampler_matches_regular_entry_point_twice(built_lib):
     finally:
         torch.cuda.synchronize()
         ctx.close()
+
+
+def test_static_sampler_matches_torch_golden_and_c_restatement(built_lib, golden_dir):
+    """Not only equal to the library's other entry point: equal to what torch's DistributedSampler
+    gave for the reference's own configuration (tests/golden/sampler_mnist_ws2.npz, made by
+    oracle/make_golden.py), and to the plain-C restatement on a second geometry."""
+    from oracle import sampler_oracle
+    torch.cuda.set_device(0)
+    g = np.load(os.path.join(golden_dir, "sampler_mnist_ws2.npz"))
+    out = torch.empty(30000, dtype=torch.int64, device="cuda")
+    for rank in (0, 1):
+        assert _static_call(out, 60000, 2, rank, 0, 0) == 0, _lib.last_error()
+        assert np.array_equal(out.cpu().numpy(), g[f"r{rank}"].astype(np.int64))
+    for n, world, rank, seed, epoch, drop_last in ((50000, 8, 5, 3, 1, False), (10007, 3, 2, 0, 4, True), (65536, 4, 0, 9, 0, False)):
+        want = sampler_oracle.c_distributed_sampler_indices(n, world, rank, seed=seed, epoch=epoch, drop_last=drop_last)
+        got = torch.empty(len(want), dtype=torch.int64, device="cuda")
+        assert _static_call(got, n, world, rank, seed, epoch, drop_last=drop_last) == 0, _lib.last_error()
+        assert np.array_equal(got.cpu().numpy(), np.asarray(want, dtype=np.int64))
 
 
 def test_static_sampler_refuses_what_does_not_fit(built_lib):

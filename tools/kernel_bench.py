@@ -25,6 +25,8 @@ def main():
     ap.add_argument("--json", default="")
     ap.add_argument("--only", default="", help="comma list of kernel names to run")
     ap.add_argument("--no-torch", action="store_true")
+    ap.add_argument("--variants", action="store_true",
+                    help="also sweep the launch settings: copy_unroll 2/4/8 x pdl 0/1 for pack/unpack, pdl 0/1 for the update")
     args = ap.parse_args()
     import torch
     import b200ddp
@@ -43,8 +45,24 @@ def main():
     kt = bench.KernelTimer(ctx, numels, dev, peak)
     only = [s for s in args.only.split(",") if s]
     out = {"model": args.model, "P": P, "tensors": len(numels), "peak_gbs": peak,
-           "pack_nb": os.environ.get("B200DDP_PACK_NB", "default"), "update_nb": os.environ.get("B200DDP_UPDATE_NB", "default"),
+           "settings": {k: ctx.get_option(k) for k in ("copy_unroll", "pdl", "div_mode")},
            "kernels": kt.all(only)}
+    if args.variants:
+        out["variants"] = []
+        default = {k: ctx.get_option(k) for k in ("copy_unroll", "pdl")}
+        for pdl in (0, 1):
+            for unroll in (2, 4, 8):
+                ctx.set_option("pdl", pdl).set_option("copy_unroll", unroll)
+                kt.close()                      # plans carry the copy chunk size: rebuild them
+                kt.plans = {}
+                names = ["pack_fp32", "pack_bf16", "unpack_fp32"] + (["update_direct", "update_from_bucket_write_grad"]
+                                                                    if unroll == 4 else [])
+                row = {"pdl": pdl, "copy_unroll": unroll, "kernels": kt.all(names)}
+                out["variants"].append(row)
+                print("variant", json.dumps(row), flush=True)
+        ctx.set_option("pdl", default["pdl"]).set_option("copy_unroll", default["copy_unroll"])
+        kt.close()
+        kt.plans = {}
     for k, v in out["kernels"].items():
         print(k, v, flush=True)
     if not args.no_torch and not only:
