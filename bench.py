@@ -53,6 +53,11 @@ def parse():
                     help="fused: sync folded into optimizer.step(); strict: p.grad averaged first")
     ap.add_argument("--step", default="graph", choices=["graph", "eager"],
                     help="graph: the loop body replayed from a CUDA graph; eager: the reference's Python loop")
+    ap.add_argument("--overlap", default="auto", choices=["auto", "on", "off"],
+                    help="start each bucket's pack + all-reduce from inside backward (auto: on when N > 1)")
+    ap.add_argument("--no-parity-check", action="store_true", help="skip the N > 1 self-check against NCCL / exact sums")
+    ap.add_argument("--no-torch-baseline", action="store_true",
+                    help="skip timing the reference's own GPU path (per-parameter NCCL all_reduce + torch.optim.SGD)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--settle", type=int, default=10,
                     help="untimed set-up steps BEFORE the warm-up: cuDNN autotune, allocator growth, momentum "
@@ -429,6 +434,199 @@ def kernel_microbench(ctx, params, peak_gbs, only=None):
         kt.close()
 
 
+
+# --------------------------------------------------------------------------- multi-GPU self-check (outside the timed region)
+def _exact_grads(torch, numels, rank, step, dev):
+    """Gradients on a coarse binary grid (an integer in [-4096, 4096) times 2**-20): any sum of up to
+    1024 of them and its division by a power of two is exact in fp32, in every order - so every rank can
+    compute the bits the averaged gradient MUST have without communicating.  Returns (per-tensor floats,
+    per-tensor int64 values)."""
+    fl, iv = [], []
+    for t, n in enumerate(numels):
+        i = torch.arange(n, device=dev, dtype=torch.int64)
+        v = ((i * 2654435761 + (rank + 1) * 40503 + (t + 1) * 9973 + step * 7919) >> 7) % 8192 - 4096
+        iv.append(v)
+        fl.append(v.to(torch.float32) * (2.0 ** -20))
+    return fl, iv
+
+
+def parity_check(torch, dist, b200ddp, numels, world, rank, dev, bucket_dtype):
+    """The real multi-process path against what the reference's sync must produce
+    (codes/task2/dist_utils.py:39-42), through every reduction algorithm available at this world size:
+    (i) exact-sum gradients, strict and fused, compared BIT FOR BIT with the locally computed mean;
+    (ii) dense gradients against torch's NCCL all_reduce + division, rel <= 1e-5 (north-star bound);
+    (iii) bf16 buckets against the fp32 result, rel <= 2**-7."""
+    ctx = b200ddp.default_context()
+    GradSync = b200ddp.GradSync
+    pow2 = world & (world - 1) == 0
+    algos = ["twoshot", "oneshot"] + (["nvls"] if ctx.has_multicast else []) + (["nccl"] if ctx.has_nccl else [])
+    report = {"algos": {}, "world": world, "tensors": len(numels), "elements": int(sum(numels)),
+              "multicast": bool(ctx.has_multicast)}
+    fake = [torch.nn.Parameter(torch.zeros(n, device=dev)) for n in numels]
+    lr = 0.01
+    ok_all = True
+
+    def agree(flag):
+        t = torch.tensor([1 if flag else 0], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
+
+    # expected mean of the exact gradients (every rank computes all ranks' inputs)
+    step = 3
+    total = None
+    for r in range(world):
+        _, iv = _exact_grads(torch, numels, r, step, dev)
+        total = iv if total is None else [a + b for a, b in zip(total, iv)]
+    want = [(v.to(torch.float32) * (2.0 ** -20)) / world for v in total]
+    mine, _ = _exact_grads(torch, numels, rank, step, dev)
+    # what the update must leave: the library's own direct update (checked bit for bit against torch.optim.SGD by
+    # the single-GPU tests) fed the expected mean
+    p0 = [torch.full((n,), 0.25, device=dev) for n in numels]
+    p_want = [t.clone() for t in p0]
+    m_want = [torch.empty_like(t) for t in p0]
+    plan = ctx.plan(numels)
+    ctx.sgd_step(plan, [t.data_ptr() for t in want], [t.data_ptr() for t in p_want], [t.data_ptr() for t in m_want],
+                 b200ddp.sgd_args(lr=lr, momentum=0.9, first_step=True))
+    plan.close()
+    torch.cuda.synchronize()
+    cases = [(a, False) for a in algos] + [("auto", True)]          # the last one is the timed configuration
+    for algo, overlap in cases:
+        name = algo + ("+overlap" if overlap else "")
+        entry = {}
+        # (i) strict
+        eng = GradSync(fake, ctx, "fp32", algo, overlap=overlap)
+        for p, g in zip(fake, mine):
+            p.grad = g.clone()
+        eng.sync()
+        torch.cuda.synchronize()
+        entry["strict_exact_bits"] = agree(pow2 and all(torch.equal(p.grad, w) for p, w in zip(fake, want)))
+        # (i) fused with the update
+        with torch.no_grad():
+            for p, q in zip(fake, p0):
+                p.copy_(q)
+        for p, g in zip(fake, mine):
+            p.grad = g.clone()
+        moms = [torch.empty_like(p) for p in fake]
+        eng.sync_and_step(moms, dict(lr=lr, momentum=0.9), first_step=True, write_grads=True)
+        torch.cuda.synchronize()
+        entry["fused_exact_bits"] = agree(pow2 and all(torch.equal(p.detach(), w) for p, w in zip(fake, p_want))
+                                          and all(torch.equal(m, w) for m, w in zip(moms, m_want))
+                                          and all(torch.equal(p.grad, w) for p, w in zip(fake, want)))
+        picked = sorted({b.algo for b in eng.buckets if b.algo is not None})
+        names = {v: k for k, v in b200ddp._lib.ALGO_NAMES.items()}
+        entry["kernels_used"] = [names[a] for a in picked]
+        entry["buckets"] = len(eng.buckets)
+        # (ii) dense gradients against NCCL
+        gen = torch.Generator(device=dev).manual_seed(100 + rank)
+        dense = [torch.randn(n, device=dev, generator=gen) * 1e-2 for n in numels]
+        ref = [d.clone() for d in dense]
+        for t in ref:                       # codes/task2/dist_utils.py:40-42 on the GPU
+            dist.all_reduce(t, op=dist.ReduceOp.SUM)
+            t /= world
+        for p, g in zip(fake, dense):
+            p.grad = g.clone()
+        eng.sync()
+        torch.cuda.synchronize()
+        num = max(float((p.grad - r).abs().max()) for p, r in zip(fake, ref) if r.numel())
+        den = max(float(r.abs().max()) for r in ref if r.numel())
+        entry["dense_rel_vs_nccl"] = num / den
+        t = torch.tensor([num / den], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        entry["dense_rel_vs_nccl"] = float(t.item())
+        # all ranks hold the same bits
+        flat = torch.cat([p.grad.reshape(-1) for p in fake])
+        ref0 = flat.clone()
+        dist.broadcast(ref0, 0)
+        entry["ranks_identical"] = agree(torch.equal(flat, ref0))
+        entry["ok"] = bool(entry["strict_exact_bits"] and entry["fused_exact_bits"] and entry["ranks_identical"]
+                           and entry["dense_rel_vs_nccl"] <= 1e-5)
+        ok_all = ok_all and entry["ok"]
+        report["algos"][name] = entry
+        eng.close()
+        if algo == "auto":
+            # (iii) bf16 buckets: same dense gradients, against the fp32 NCCL result
+            eng = GradSync(fake, ctx, "bf16", "auto", overlap=overlap)
+            for p, g in zip(fake, dense):
+                p.grad = g.clone()
+            eng.sync()
+            torch.cuda.synchronize()
+            num = max(float((p.grad - r).abs().max()) for p, r in zip(fake, ref) if r.numel())
+            t = torch.tensor([num / den], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            report["bf16_rel_vs_fp32"] = float(t.item())
+            report["bf16_bound"] = 2.0 ** -7
+            ok_all = ok_all and report["bf16_rel_vs_fp32"] <= 2.0 ** -7
+            eng.close()
+    report["ok"] = bool(ok_all)
+    report["bounds"] = {"exact": "bit for bit (integer-grid gradients)", "dense_rel": 1e-5}
+    return report
+
+
+def torch_gpu_baseline(torch, dist, b200ddp, name, lr, world, dev, dev_batches, loss_fn, batch, steps, warmup, settle,
+                       fence):
+    """What this repo's kernels are up against on the same GPU(s): the reference's sync exactly as written -
+    one NCCL all_reduce and one division per parameter (codes/task2/dist_utils.py:39-42, backend "nccl" as :12
+    hard-codes) - and torch.optim.SGD (codes/task2/model.py:131), forward/backward identical.  Timed eagerly (the
+    reference's Python loop) and replayed from the same CUDA-graph wrapper the b200 arm uses."""
+    model, _, _ = build_model(name)
+    model = model.to(dev).train()
+    if world > 1:
+        for p in model.parameters():            # codes/task2/dist_utils.py:33-37
+            dist.broadcast(p.data, 0)
+    opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=0.9)
+
+    def ref_sync(m):
+        if world > 1:
+            for p in m.parameters():
+                dist.all_reduce(p.grad.data, op=dist.ReduceOp.SUM)
+                p.grad.data /= world
+
+    def eager_step(i):
+        x, y = dev_batches[i % len(dev_batches)]
+        loss = loss_fn(model(x), y)
+        opt.zero_grad()
+        loss.backward()
+        ref_sync(model)
+        opt.step()
+        return loss
+
+    def timed(fn):
+        fence()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(steps):
+            fn(i)
+        b.record()
+        fence()
+        t = torch.tensor([a.elapsed_time(b) * 1e-3], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    out = {"what": "per-parameter NCCL all_reduce + division + torch.optim.SGD (foreach), same model and batches"}
+    for i in range(settle + warmup):
+        eager_step(i)
+    t = timed(eager_step)
+    out["eager_ms_per_step"] = t / steps * 1e3
+    out["eager_samples_per_s"] = world * batch * steps / t
+    try:
+        g = b200ddp.GraphedTrainStep(model, loss_fn, opt, sync=ref_sync, eager_steps=1)
+        gs = lambda i: g(*dev_batches[i % len(dev_batches)])
+        for i in range(3 + warmup):
+            gs(i)
+        if g.graph is None:
+            raise RuntimeError(f"capture failed: {g.capture_error}")
+        t = timed(gs)
+        out["graph_ms_per_step"] = t / steps * 1e3
+        out["samples_per_s"] = world * batch * steps / t
+    except Exception as e:                      # NCCL under capture is the usual suspect; keep the eager number
+        out["graph_ms_per_step"] = None
+        out["samples_per_s"] = out["eager_samples_per_s"]
+        out["graph_error"] = str(e)[:300]
+        torch.cuda.synchronize()
+    return out
+
+
 def gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -452,7 +650,8 @@ def gpu_arm(args):
     name, batch, lr = MODELS[args.model]
     batch = args.batch or batch
     bucket_dtype = args.bucket_dtype or ("bf16" if args.model == "resnet50" else "fp32")
-    b200ddp.configure(bucket_dtype=bucket_dtype, algo=args.algo)
+    overlap = world > 1 and args.overlap != "off"
+    b200ddp.configure(bucket_dtype=bucket_dtype, algo=args.algo, overlap=overlap)
 
     model, chw, classes = build_model(name)
     model = model.to(dev).train()
@@ -471,6 +670,12 @@ def gpu_arm(args):
 
     def total_launches():
         return opt.launches + (b200ddp.dist_utils.engine_for(model).launches if args.mode == "strict" else 0)
+
+    parity = None
+    if world > 1 and not args.no_parity_check:
+        parity = parity_check(torch, dist, b200ddp, [p.numel() for p in params], world, rank, dev, bucket_dtype)
+        if rank == 0:
+            print("parity_check:", json.dumps(parity), file=sys.stderr, flush=True)
 
     gstep = b200ddp.GraphedTrainStep(model, loss_fn, opt) if args.step == "graph" else None
     graph_info = {"launches_per_step": None}
@@ -542,6 +747,12 @@ def gpu_arm(args):
         t_eager = timed(False, args.steps, record=True, eager=True)
     ours_s = statistics.mean(a.elapsed_time(b) for a, b in k3) * 1e-3 if k3 else None
 
+    # ---- the kernel-to-beat: the reference's own GPU path on the same model, batches and timing
+    torch_base = None
+    if not args.no_torch_baseline:
+        torch_base = torch_gpu_baseline(torch, dist, b200ddp, name, lr, world, dev, dev_batches, loss_fn, batch,
+                                        args.steps, args.warmup, max(args.settle, 4), fence)
+
     # ---- the dominant kernel of ours, against the measured HBM peak
     peaks = {}
     try:
@@ -554,28 +765,43 @@ def gpu_arm(args):
         # grad-sync bus bandwidth on this model's own bucket(s): 20 reductions back to back,
         # max over ranks, busbw = S / t * 2 (N - 1) / N (nccl-tests convention)
         eng = b200ddp.dist_utils.engine_for(model)
-        S = sum(bk.plan.bucket_bytes for bk in eng.buckets)
         names = {v: k for k, v in b200ddp._lib.ALGO_NAMES.items()}
-        picked = sorted({names[eng.ctx.allreduce_pick(bk.plan.bucket_elems, eng.dtype)] if args.algo == "auto"
-                         else args.algo for bk in eng.buckets})
-        for _ in range(3):
-            for bk in eng.buckets:
-                eng.ctx.allreduce(bk.offset, bk.plan.bucket_elems, eng.dtype, args.algo)
-        fence()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        for _ in range(20):
-            for bk in eng.buckets:
-                eng.ctx.allreduce(bk.offset, bk.plan.bucket_elems, eng.dtype, args.algo)
-        b.record()
-        fence()
-        t = torch.tensor([a.elapsed_time(b) * 1e-3 / 20], device=dev, dtype=torch.float64)
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        t = float(t.item())
-        extras["grad_sync"] = {"bucket_bytes": S, "buckets": len(eng.buckets), "algo": picked, "us": t * 1e6,
-                               "algbw_gbs": S / t / 1e9, "busbw_gbs": S / t / 1e9 * 2 * (world - 1) / world,
-                               "nvlink_peak_gbs_per_direction": 900.0,
-                               "frac_of_nominal_nvlink": S / t / 1e9 * 2 * (world - 1) / world / 900.0}
+        esize = 2 if bucket_dtype == "bf16" else 4
+
+        def reduce_time(pieces):
+            """pieces: [(staging offset, elements)] reduced one after the other, 20 rounds, max over ranks."""
+            for _ in range(3):
+                for off, n in pieces:
+                    eng.ctx.allreduce(off, n, eng.dtype, args.algo)
+            fence()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(20):
+                for off, n in pieces:
+                    eng.ctx.allreduce(off, n, eng.dtype, args.algo)
+            b.record()
+            fence()
+            t = torch.tensor([a.elapsed_time(b) * 1e-3 / 20], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+
+        def bus(S, t, pieces):
+            picked = sorted({names[eng.ctx.allreduce_pick(n, eng.dtype)] if args.algo == "auto" else args.algo
+                             for _, n in pieces})
+            return {"bucket_bytes": S, "buckets": len(pieces), "algo": picked, "us": t * 1e6,
+                    "algbw_gbs": S / t / 1e9, "busbw_gbs": S / t / 1e9 * 2 * (world - 1) / world,
+                    "nvlink_peak_gbs_per_direction": 900.0,
+                    "frac_of_nominal_nvlink": S / t / 1e9 * 2 * (world - 1) / world / 900.0}
+
+        # grad-sync bus bandwidth, busbw = S / t * 2 (N - 1) / N (nccl-tests convention):
+        # the model's gradients as ONE flat bucket (the K2 kernel on the size SURVEY.md section 8 names) ...
+        flat_elems = sum(b200ddp.engine.padded_numel(p.numel()) for p in params)
+        flat = [(0, flat_elems)]
+        extras["grad_sync"] = bus(flat_elems * esize, reduce_time(flat), flat)
+        # ... and as the buckets the step really uses (cut for overlap with backward)
+        pieces = [(bk.offset, bk.plan.bucket_elems) for bk in eng.buckets]
+        if len(pieces) > 1:
+            extras["grad_sync_bucketed"] = bus(sum(n for _, n in pieces) * esize, reduce_time(pieces), pieces)
     if rank == 0:
         ctx = b200ddp.default_context()
         if not args.no_kernel_bench:
@@ -606,18 +832,20 @@ def gpu_arm(args):
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
-        return 0
+        return 0 if (parity is None or parity["ok"]) else 1
     line = {"metric": METRIC, "value": world * batch * args.steps / t_dev, "unit": UNIT, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3,
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args.model, batch, world),
             "arm": {"where": f"{world} x B200, one process per GPU", "bucket_dtype": bucket_dtype, "mode": args.mode,
-                    "algo": args.algo, "settle_steps": settle},
+                    "algo": args.algo, "settle_steps": settle, "overlap": overlap,
+                    "buckets": len(b200ddp.dist_utils.engine_for(model).buckets)},
             "e2e": {"value": world * batch * args.steps / t_e2e, "unit": UNIT, "h2d_bytes_per_step": h2d,
                     "d2h_bytes_per_step": 4, "ms_per_step": t_e2e / args.steps * 1e3},
             "gpu_launches": launches, "clocks": clk, "roofline": roofline,
             "step_mode": ("cuda-graph replay of the loop body (b200ddp.GraphedTrainStep)" if graphed else
                           "eager loop" + (f" (graph capture failed: {gstep.capture_error})" if gstep is not None else "")),
+            "parity_check": parity, "torch_gpu_baseline": torch_base,
             "eager_ms_per_step": t_eager / args.steps * 1e3 if t_eager else None,
             "sync_update_ms_per_step_eager": ours_s * 1e3 if ours_s else None}
     line.update(extras)
@@ -626,7 +854,7 @@ def gpu_arm(args):
     emit(line)
     if world > 1:
         dist.destroy_process_group()
-    return 0
+    return 0 if (parity is None or parity["ok"]) else 1
 
 
 _REAL_STDOUT = None

@@ -17,11 +17,11 @@ from .dist_utils import (CommTimer, allgather_average_gradients, broadcast_from_
 from .engine import GradSync
 from .graph import GraphedTrainStep
 from .hooks import HookState, comm_hook
-from .optim import SGD
-from .runtime import Context, Plan, default_context, reset_default_context, sampler_sizes, sgd_args
+from .optim import SGD, AdamOptimizer, BaseOptimizer, GdOptimizer
+from .runtime import Context, Plan, default_context, opt_args, reset_default_context, sampler_sizes, sgd_args
 from .sampler import DistributedSampler, MySampler
 
-__all__ = ["B200DDPError", "Context", "Plan", "GradSync", "GraphedTrainStep", "SGD", "DistributedSampler", "MySampler", "HookState",
+__all__ = ["B200DDPError", "Context", "Plan", "GradSync", "GraphedTrainStep", "SGD", "AdamOptimizer", "GdOptimizer", "BaseOptimizer", "DistributedSampler", "MySampler", "HookState",
            "comm_hook", "dist_utils", "dist_init", "get_local_rank", "get_world_size", "init_parameters",
            "allreduce_average_gradients", "average_gradients", "allgather_average_gradients", "enable_fused_step",
-           "configure", "CommTimer", "broadcast_from_rank0", "default_context", "reset_default_context", "sampler_sizes", "sgd_args"]
+           "configure", "CommTimer", "broadcast_from_rank0", "default_context", "reset_default_context", "sampler_sizes", "sgd_args", "opt_args"]

@@ -66,12 +66,15 @@ _SIGNATURES = {
     "b200ddp_ipc_open_peers": (c_int, [c_void_p, c_void_p]),
     "b200ddp_set_peers_direct": (c_int, [c_void_p, _PP, _PP]),
     "b200ddp_adopt_symmetric": (c_int, [c_void_p, _PP, c_void_p, c_size_t]),
+    "b200ddp_free_retired": (c_int, [c_void_p]),
+    "b200ddp_close_peers": (c_int, [c_void_p]),
     "b200ddp_plan_create": (c_int, [c_void_p, c_int, POINTER(c_int64), c_int, POINTER(c_void_p)]),
     "b200ddp_plan_destroy": (c_int, [c_void_p]),
     "b200ddp_plan_bucket_elems": (c_int64, [c_void_p]),
     "b200ddp_plan_offsets": (c_int, [c_void_p, POINTER(c_int64)]),
     "b200ddp_pack_scale": (c_int, [c_void_p, c_void_p, _PP, c_void_p, c_float, c_void_p]),
     "b200ddp_allreduce": (c_int, [c_void_p, c_size_t, c_int64, c_int, c_int, c_void_p, POINTER(c_size_t)]),
+    "b200ddp_barrier": (c_int, [c_void_p, c_void_p]),
     "b200ddp_allreduce_pick": (c_int, [c_void_p, c_int64, c_int]),
     "b200ddp_unpack": (c_int, [c_void_p, c_void_p, c_void_p, _PP, c_float, c_void_p]),
     "b200ddp_unpack_sgd": (c_int, [c_void_p, c_void_p, c_void_p, _PP, _PP, _PP, POINTER(SgdArgs), c_void_p]),

@@ -215,18 +215,49 @@ int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200dd
     return B200DDP_OK;
 }
 
-int b200ddp_destroy(b200ddp_ctx *ctx) {
-    if (!ctx) return B200DDP_OK;
-    cudaSetDevice(ctx->device);
-    cudaDeviceSynchronize();
-    nccl_destroy(ctx);
+static void close_peer_mappings(b200ddp_ctx *ctx) {
     if (ctx->peers_ipc) {
         for (int r = 0; r < ctx->world; ++r) {
             if (r == ctx->rank) continue;
             if (ctx->peers.staging[r] && !ctx->staging_external) cudaIpcCloseMemHandle(ctx->peers.staging[r]);
             if (ctx->peers.flags[r]) cudaIpcCloseMemHandle(ctx->peers.flags[r]);
+            ctx->peers.staging[r] = nullptr;
+            ctx->peers.flags[r] = nullptr;
         }
+        ctx->peers_ipc = false;
+        ctx->peers_ready = false;
     }
+}
+
+int b200ddp_close_peers(b200ddp_ctx *ctx) {
+    B2_REQUIRE(ctx != nullptr, B200DDP_EINVAL, "ctx is NULL");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+    B2_CHECK_CUDA(cudaDeviceSynchronize());
+    close_peer_mappings(ctx);
+    cudaGetLastError();
+    return B200DDP_OK;
+}
+
+int b200ddp_free_retired(b200ddp_ctx *ctx) {
+    B2_REQUIRE(ctx != nullptr, B200DDP_EINVAL, "ctx is NULL");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    if (ctx->retired_staging) {
+        B2_CHECK_CUDA(cudaSetDevice(ctx->device));
+        cudaFree(ctx->retired_staging);
+        ctx->retired_staging = nullptr;
+        cudaGetLastError();
+    }
+    return B200DDP_OK;
+}
+
+int b200ddp_destroy(b200ddp_ctx *ctx) {
+    if (!ctx) return B200DDP_OK;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    nccl_destroy(ctx);
+    close_peer_mappings(ctx);
+    cudaFree(ctx->retired_staging);
     cudaFree(ctx->sampler_scratch);
     cudaFree(ctx->trace);
     if (!ctx->staging_external) cudaFree(ctx->staging);
@@ -381,8 +412,10 @@ int b200ddp_adopt_symmetric(b200ddp_ctx *ctx, void *const *peer_ptrs, void *mc_p
     if (ctx->peers_ipc)
         for (int r = 0; r < ctx->world; ++r)
             if (r != ctx->rank && ctx->peers.staging[r]) cudaIpcCloseMemHandle(ctx->peers.staging[r]);
-    cudaFree(ctx->staging);
-    cudaGetLastError();
+    // The old staging area was exported over CUDA IPC and a peer may still have it mapped: it is
+    // only retired here and freed by b200ddp_free_retired, which the caller invokes after a
+    // cross-rank barrier (every rank has closed its mappings by then).
+    ctx->retired_staging = ctx->staging;
     ctx->staging_external = true;
     ctx->staging = (char *)peer_ptrs[ctx->rank];
     for (int r = 0; r < ctx->world; ++r) ctx->peers.staging[r] = (char *)peer_ptrs[r];
@@ -638,6 +671,14 @@ int b200ddp_allreduce(b200ddp_ctx *ctx, size_t offset_bytes, int64_t nelem, int 
     B2_REQUIRE(algo == B200DDP_ALGO_ONESHOT || algo == B200DDP_ALGO_TWOSHOT, B200DDP_EINVAL, "bad algo %d", algo);
     if (algo == B200DDP_ALGO_ONESHOT && result_offset_bytes) *result_offset_bytes = ctx->staging_bytes + offset_bytes;
     return launch_p2p_allreduce(ctx, offset_bytes, nelem, dtype, algo, s);
+}
+
+int b200ddp_barrier(b200ddp_ctx *ctx, b200ddp_stream stream) {
+    B2_REQUIRE(ctx != nullptr, B200DDP_EINVAL, "ctx is NULL");
+    if (ctx->world == 1) return B200DDP_OK;
+    B2_REQUIRE(ctx->peers_ready, B200DDP_ESTATE, "peer memory not opened");
+    std::lock_guard<std::mutex> lk(ctx->mu);
+    return launch_barrier(ctx, (cudaStream_t)stream);
 }
 
 int b200ddp_allreduce_sgd(b200ddp_ctx *ctx, b200ddp_plan *plan, size_t offset_bytes, void *const *params,

@@ -139,6 +139,7 @@ struct b200ddp_ctx {
     size_t staging_bytes = 0;          // one half
     char *staging = nullptr;           // 2 x staging_bytes
     bool staging_external = false;     // adopted symmetric memory: owned by the caller
+    char *retired_staging = nullptr;   // own IPC-exported staging replaced by symmetric memory, not yet freed
     char *mc_ptr = nullptr;            // multicast address over every rank's staging (NVLS), or null
     uint32_t *flags = nullptr;         // peer-visible: kMaxBlocksP2P x MAX_WORLD
     uint32_t *block_gen = nullptr;     // local: barrier generation of each block index, advanced by the kernels
@@ -201,6 +202,7 @@ int launch_update(const b200ddp_plan *plan, const void *bucket /*null: direct*/,
 // p2p.cu
 int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int block_cap);
 int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, int algo, cudaStream_t s);
+int launch_barrier(b200ddp_ctx *ctx, cudaStream_t s);
 int launch_nvls_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, cudaStream_t s);
 int launch_p2p_allreduce_emu(b200ddp_ctx *const *ctxs, int n, size_t off, int64_t nelem, int dtype,
                              int algo, cudaStream_t s);

@@ -332,6 +332,17 @@ __global__ void __launch_bounds__(kP2PThreads) nvls_kernel(P2PArgs a, char *mc) 
     if (threadIdx.x == 0) a.gen[rank][bid] = gen + 2;
 }
 
+// ---- a barrier on its own ------------------------------------------------------------------
+// One block: "everything this rank enqueued on the stream before this launch is visible to every
+// rank's work enqueued after it".  Used by the flat initial-weight broadcast (rank 0 packs, barrier,
+// the others read rank 0's staging, barrier) in place of host synchronisation + a process-group barrier.
+__global__ void __launch_bounds__(32) barrier_kernel(P2PArgs a) {
+    pdl_prologue();
+    const uint32_t gen = a.gen[a.rank][0];
+    peer_barrier(a.pt, a.rank, a.world, 0, gen + 1, a.timeout_ns);
+    if (threadIdx.x == 0) a.gen[a.rank][0] = gen + 1;
+}
+
 // ---- fused one-shot reduce + update --------------------------------------------
 // Tensor tables come by value in the kernel parameters (see TensorTab); under EMU every
 // emulated rank has its own table and its own chunk list.
@@ -465,6 +476,14 @@ int block_cap(const b200ddp_ctx *ctx) {
     int cap = ctx->p2p_blocks > 0 ? ctx->p2p_blocks : 2 * ctx->sm_count;
     return cap < kMaxBlocksP2P ? cap : kMaxBlocksP2P;
 }
+// Blocks that spin on their peers should all be resident: never launch more than the GPU can hold
+// at once (same GPUs on every rank, so every rank computes the same clamp).
+template <typename K> int resident_clamp(const b200ddp_ctx *ctx, K kernel, int threads, int grid) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    const int fit = per_sm * ctx->sm_count;
+    return grid < fit ? grid : fit;
+}
 int update_grid(const b200ddp_ctx *ctx, int nchunks) {
     const int cap = block_cap(ctx);
     return nchunks < cap ? nchunks : cap;
@@ -478,7 +497,8 @@ int run_fused(b200ddp_ctx *ctx, const b200ddp_plan *plan, const Segment &sg, siz
     fill_update_tab(ts.t[0], plan, sg, pa);
     ts.chunks[0] = plan->d_chunks + sg.c0;
     const int n = sg.c1 - sg.c0;
-    B2_LAUNCH_RC(launch_ex(oneshot_update_kernel<BT, WG, false, CAP>, update_grid(ctx, n), kThreads, s, ctx->pdl, a, ts, n, hp));
+    const int grid = resident_clamp(ctx, oneshot_update_kernel<BT, WG, false, CAP>, kThreads, update_grid(ctx, n));
+    B2_LAUNCH_RC(launch_ex(oneshot_update_kernel<BT, WG, false, CAP>, grid, kThreads, s, ctx->pdl, a, ts, n, hp));
     return B200DDP_OK;
 }
 
@@ -504,18 +524,25 @@ int p2p_grid_for(int64_t nelem, int dtype, int algo, int world, int cap) {
 
 int launch_p2p_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, int algo, cudaStream_t s) {
     P2PArgs a = make_args(ctx, off, nelem, dtype);
-    const int grid = p2p_grid_for(nelem, dtype, algo, ctx->world, block_cap(ctx));
-    B2_LAUNCH_RC(launch_ex(pick<false>(dtype, algo, ctx->world), grid, kP2PThreads, s, ctx->pdl, a));
+    P2PKernel k = pick<false>(dtype, algo, ctx->world);
+    const int grid = resident_clamp(ctx, k, kP2PThreads, p2p_grid_for(nelem, dtype, algo, ctx->world, block_cap(ctx)));
+    B2_LAUNCH_RC(launch_ex(k, grid, kP2PThreads, s, ctx->pdl, a));
+    return B200DDP_OK;
+}
+
+int launch_barrier(b200ddp_ctx *ctx, cudaStream_t s) {
+    P2PArgs a = make_args(ctx, 0, 0, B200DDP_F32);
+    B2_LAUNCH_RC(launch_ex(barrier_kernel, 1, 32, s, ctx->pdl, a));
     return B200DDP_OK;
 }
 
 int launch_nvls_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, cudaStream_t s) {
     P2PArgs a = make_args(ctx, off, nelem, dtype);
-    const int grid = p2p_grid_for(nelem, dtype, B200DDP_ALGO_NVLS, ctx->world, block_cap(ctx));
+    const int want = p2p_grid_for(nelem, dtype, B200DDP_ALGO_NVLS, ctx->world, block_cap(ctx));
     cudaError_t e;
-#define B2_NVLS(D)                                                                                              \
-    (dtype == B200DDP_F32 ? launch_ex(nvls_kernel<float, D>, grid, kP2PThreads, s, ctx->pdl, a, ctx->mc_ptr)    \
-                          : launch_ex(nvls_kernel<__nv_bfloat16, D>, grid, kP2PThreads, s, ctx->pdl, a, ctx->mc_ptr))
+#define B2_NVLS_T(BT, D) \
+    launch_ex(nvls_kernel<BT, D>, resident_clamp(ctx, nvls_kernel<BT, D>, kP2PThreads, want), kP2PThreads, s, ctx->pdl, a, ctx->mc_ptr)
+#define B2_NVLS(D) (dtype == B200DDP_F32 ? B2_NVLS_T(float, D) : B2_NVLS_T(__nv_bfloat16, D))
     switch (nvls_depth(ctx)) {
         case 1: e = B2_NVLS(1); break;
         case 2: e = B2_NVLS(2); break;
@@ -523,6 +550,7 @@ int launch_nvls_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype
         default: e = B2_NVLS(4); break;
     }
 #undef B2_NVLS
+#undef B2_NVLS_T
     B2_LAUNCH_RC(e);
     return B200DDP_OK;
 }

@@ -20,18 +20,33 @@ from .runtime import default_context
 _ENGINES: "weakref.WeakKeyDictionary[torch.nn.Module, GradSync]" = weakref.WeakKeyDictionary()
 _GATHER_ENGINES: "weakref.WeakKeyDictionary[torch.nn.Module, GradSync]" = weakref.WeakKeyDictionary()
 _CONFIG = {"bucket_dtype": os.environ.get("B200DDP_BUCKET_DTYPE", "fp32"),
-           "algo": os.environ.get("B200DDP_ALGO", "auto")}
+           "algo": os.environ.get("B200DDP_ALGO", "auto"),
+           "overlap": os.environ.get("B200DDP_OVERLAP", "0") not in ("0", "", "false"),
+           "bucket_cap_bytes": int(float(os.environ["B200DDP_BUCKET_CAP_MB"]) * (1 << 20))
+           if os.environ.get("B200DDP_BUCKET_CAP_MB") else None}
 
 
-def configure(bucket_dtype=None, algo=None):
-    """Wire dtype ("fp32" | "bf16") and reduction algorithm ("auto" | "nccl" |
-    "oneshot" | "twoshot") used by engines created afterwards."""
+def configure(bucket_dtype=None, algo=None, overlap=None, bucket_cap_bytes=None):
+    """Settings of the engines created afterwards: wire dtype ("fp32" | "bf16"), reduction algorithm
+    ("auto" | "nccl" | "oneshot" | "twoshot" | "nvls"), and overlap.
+
+    overlap=True starts pack + all-reduce of each bucket (reverse parameter order, bucket_cap_bytes
+    each, default 25 MiB like torch DDP) from inside backward on a side stream; the call to
+    allreduce_average_gradients(model) then only joins and unpacks.  Same values as the plain path
+    PROVIDED p.grad is not modified between backward and the sync call (what left early would be
+    stale) - the reference's loop does not (codes/task2/model.py:58-62).  Off by default."""
     if bucket_dtype is not None:
         _CONFIG["bucket_dtype"] = bucket_dtype
     if algo is not None:
         if algo not in _lib.ALGO_NAMES:
             raise ValueError(f"algo must be one of {sorted(_lib.ALGO_NAMES)}")
         _CONFIG["algo"] = algo
+    if overlap is not None:
+        _CONFIG["overlap"] = bool(overlap)
+    if bucket_cap_bytes is not None:
+        _CONFIG["bucket_cap_bytes"] = int(bucket_cap_bytes) or None
+    for eng in list(_ENGINES.values()) + list(_GATHER_ENGINES.values()):
+        eng.close()
     _ENGINES.clear()
     _GATHER_ENGINES.clear()
 
@@ -61,34 +76,36 @@ def get_world_size():
     return dist.get_world_size() if dist.is_initialized() else 1
 
 
-def broadcast_from_rank0(tensors):
+def broadcast_from_rank0(tensors, ctx=None):
     """Rank 0's values of `tensors` to every rank, as flat buckets: rank 0 packs them into
     its staging area, the other ranks unpack straight out of rank 0's memory over NVLink
     (one pack + one unpack per bucket instead of one NCCL broadcast per tensor).
     fp32 CUDA tensors take this path; anything else (e.g. BatchNorm's int64
     num_batches_tracked) falls back to torch.distributed.broadcast."""
     from .engine import split_buckets
-    ctx = default_context()
+    ctx = ctx if ctx is not None else default_context()
     flat = [t for t in tensors if t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()]
     flat_ids = {id(t) for t in flat}
     for t in tensors:
         if id(t) not in flat_ids:
-            dist.broadcast(t, 0)
-    if not flat:
+            dist.broadcast(t, dist.get_global_rank(ctx._group, 0) if ctx._group is not None else 0, group=ctx._group)
+    if not flat or ctx.world == 1:
         return
     numels = [t.numel() for t in flat]
     for lo, hi, off, _ in split_buckets(numels, 4, None, ctx.staging_bytes):
-        plan = ctx.plan(numels[lo:hi])
+        key = tuple(numels[lo:hi])
+        plan = ctx._bcast_plans.get(key)
+        if plan is None:
+            plan = ctx._bcast_plans[key] = ctx.plan(numels[lo:hi])
         ptrs = [t.data_ptr() for t in flat[lo:hi]]
+        # everything is stream-ordered; the two device-side barriers (one tiny kernel each) replace
+        # the host synchronisation + process-group barriers of round 1
         if ctx.rank == 0:
             ctx.pack_scale(plan, ptrs, ctx.bucket_ptr(off), 1.0)
-        torch.cuda.synchronize()
-        dist.barrier()                      # rank 0's bucket is complete and visible
+        ctx.barrier()                       # rank 0's bucket is complete and visible
         if ctx.rank != 0:
             ctx.unpack(plan, ctx.peer_bucket_ptr(0, off), ptrs, 1.0)
-        torch.cuda.synchronize()
-        dist.barrier()                      # everyone has read it; the staging area may be reused
-        plan.close()
+        ctx.barrier()                       # everyone has read it; the staging area may be reused
 
 
 def init_parameters(model, buffers=False):
@@ -107,7 +124,8 @@ def engine_for(model) -> GradSync:
     eng = _ENGINES.get(model)
     if eng is None:
         eng = _ENGINES[model] = GradSync(list(model.parameters()), default_context(),
-                                         bucket_dtype=_CONFIG["bucket_dtype"], algo=_CONFIG["algo"])
+                                         bucket_dtype=_CONFIG["bucket_dtype"], algo=_CONFIG["algo"],
+                                         overlap=_CONFIG["overlap"], bucket_cap_bytes=_CONFIG["bucket_cap_bytes"])
     return eng
 
 
@@ -193,12 +211,13 @@ def enable_fused_step(model, optimizer, write_grads=True):
     averaged gradient never makes a separate round trip through p.grad.
     Between allreduce_average_gradients(model) and optimizer.step() p.grad still
     holds the LOCAL gradient; after step() it holds the mean (write_grads=True)."""
-    from .optim import SGD
-    if not isinstance(optimizer, SGD):
-        raise TypeError("enable_fused_step needs a b200ddp.SGD optimizer")
+    from .optim import SGD, BaseOptimizer
+    if not isinstance(optimizer, (SGD, BaseOptimizer)):
+        raise TypeError("enable_fused_step needs a b200ddp optimizer (SGD, AdamOptimizer, GdOptimizer)")
     eng = engine_for(model)
-    if len(optimizer.param_groups) != 1 or [id(p) for p in optimizer.param_groups[0]["params"]] != \
-            [id(p) for p in eng.params]:
+    held = optimizer.params if isinstance(optimizer, BaseOptimizer) else \
+        (optimizer.param_groups[0]["params"] if len(optimizer.param_groups) == 1 else [])
+    if [id(p) for p in held] != [id(p) for p in eng.params]:
         raise ValueError("fused step needs one param group holding model.parameters() in order")
     eng.fused_optimizer = weakref.ref(optimizer)
     optimizer._engine = eng

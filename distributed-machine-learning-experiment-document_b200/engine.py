@@ -8,13 +8,23 @@
 The parameter list is cut into buckets that fit the staging area; each bucket
 owns a plan (device chunk table) and a fixed staging offset.  Python only
 gathers `data_ptr()`s; every byte of gradient data is moved by the kernels.
+
+overlap=True starts pack + all-reduce of a bucket from inside backward, on a
+side stream, as soon as the last gradient of the bucket has been accumulated
+(post-accumulate-grad hooks): buckets are cut in REVERSE parameter order, the
+order in which backward produces gradients, so that only the last, small
+bucket (the first layers) is still in flight when backward ends.  The
+reference syncs after the whole backward (codes/task2/model.py:58-62); the
+values are the same, only the time at which the work starts differs.
 """
 from __future__ import annotations
 
 import torch
 
 from . import _lib
-from .runtime import Context, Plan, default_context, dtype_code, sgd_args
+from .runtime import Context, Plan, default_context, dtype_code, opt_args, sgd_args
+
+DEFAULT_OVERLAP_CAP = 25 << 20      # torch DDP's bucket_cap_mb, torch/nn/parallel/distributed.py
 
 
 def _is_pow2(n: int) -> bool:
@@ -59,18 +69,30 @@ def split_buckets(numels, esize: int, cap_bytes, staging_bytes: int):
     return out
 
 
+def split_buckets_reverse(numels, esize: int, cap_bytes, staging_bytes: int):
+    """The same greedy split walked from the LAST tensor to the first: bucket 0 holds the tail of
+    the list (the gradients backward produces first).  Returns [(lo, hi, staging_offset, elems)]
+    in launch order; inside a bucket the tensors keep their list order."""
+    n = len(numels)
+    rev = split_buckets(list(reversed(numels)), esize, cap_bytes, staging_bytes)
+    return [(n - hi, n - lo, off, elems) for lo, hi, off, elems in rev]
+
+
 class _Bucket:
-    __slots__ = ("lo", "hi", "plan", "offset", "result_offset", "algo")
+    __slots__ = ("lo", "hi", "plan", "offset", "result_offset", "algo", "ready", "launched", "fused_pending")
 
     def __init__(self, lo, hi, plan, offset):
         self.lo, self.hi, self.plan, self.offset = lo, hi, plan, offset
         self.result_offset = offset
         self.algo = None
+        self.ready = 0               # gradients of this bucket accumulated since the last sync
+        self.launched = False        # pack + reduce already enqueued (overlap mode)
+        self.fused_pending = False   # reduction left to the fused one-shot update
 
 
 class GradSync:
     def __init__(self, params, ctx: Context | None = None, bucket_dtype="fp32", algo="auto",
-                 bucket_cap_bytes: int | None = None):
+                 bucket_cap_bytes: int | None = None, overlap: bool = False):
         self.ctx = ctx if ctx is not None else default_context()
         self.params = [p for p in params]
         for p in self.params:
@@ -81,16 +103,38 @@ class GradSync:
         self.algo = algo
         self.world = self.ctx.world
         esize = 2 if self.dtype == _lib.BF16 else 4
+        numels = [p.numel() for p in self.params]
+        total = sum(padded_numel(n) for n in numels) * esize
+        # a list so small that one fused one-shot kernel handles it gains nothing from starting early
+        self.overlap = bool(overlap) and self.world > 1 and total > (1 << 20)
+        if self.overlap:
+            layout = split_buckets_reverse(numels, esize, bucket_cap_bytes or DEFAULT_OVERLAP_CAP, self.ctx.staging_bytes)
+        else:
+            layout = split_buckets(numels, esize, bucket_cap_bytes, self.ctx.staging_bytes)
         self.buckets: list[_Bucket] = []
-        for lo, hi, offset, elems in split_buckets([p.numel() for p in self.params], esize,
-                                                   bucket_cap_bytes, self.ctx.staging_bytes):
-            plan = self.ctx.plan([p.numel() for p in self.params[lo:hi]], self.dtype)
+        for lo, hi, offset, elems in layout:
+            plan = self.ctx.plan(numels[lo:hi], self.dtype)
             assert plan.bucket_elems == elems
             self.buckets.append(_Bucket(lo, hi, plan, offset))
         self.reuses_staging = any(b.offset == 0 for b in self.buckets[1:])
+        if self.overlap and self.reuses_staging:
+            raise _lib.B200DDPError("overlap needs every bucket resident in the staging area at once; "
+                                    "raise B200DDP_STAGING_MB")
         self.pending = False          # fused mode: sync requested, applied by optimizer.step()
-        self.fused_optimizer = None   # weakref to the b200ddp.SGD this engine is fused with
+        self.fused_optimizer = None   # weakref to the b200ddp optimizer this engine is fused with
         self.launches = 0             # kernels of ours enqueued so far
+        self._hooks = []
+        self._side = None
+        self._next = 0                # overlap: next bucket to launch (buckets go out in index order on every rank)
+        self._dirty = False           # a gradient was accumulated twice since the last sync: early results are stale
+        if self.overlap:
+            self._side = torch.cuda.Stream(device=self.params[0].device)
+            owner = {}
+            for bi, b in enumerate(self.buckets):
+                for p in self.params[b.lo:b.hi]:
+                    owner[id(p)] = bi
+            for p in self.params:
+                self._hooks.append(p.register_post_accumulate_grad_hook(self._make_hook(owner[id(p)])))
 
     # ---- helpers -----------------------------------------------------------------
     def _grads(self, b: _Bucket):
@@ -115,10 +159,10 @@ class GradSync:
             return 1.0 / n, 1.0
         return 1.0, float(n)
 
-    def _pack_and_reduce(self, b: _Bucket, grad_ptrs, fuse_oneshot: bool):
+    def _pack_and_reduce(self, b: _Bucket, grad_ptrs, fuse_oneshot: bool, stream=None):
         """Returns True if the reduction was left to a fused one-shot update."""
         scale, _ = self._scales()
-        self.ctx.pack_scale(b.plan, grad_ptrs, self.ctx.bucket_ptr(b.offset), scale)
+        self.ctx.pack_scale(b.plan, grad_ptrs, self.ctx.bucket_ptr(b.offset), scale, stream)
         self.launches += 1
         b.result_offset = b.offset
         if self.world == 1:
@@ -129,9 +173,60 @@ class GradSync:
         b.algo = algo
         if fuse_oneshot and algo == _lib.ALGO_ONESHOT:
             return True
-        b.result_offset = self.ctx.allreduce(b.offset, b.plan.bucket_elems, self.dtype, algo)
+        b.result_offset = self.ctx.allreduce(b.offset, b.plan.bucket_elems, self.dtype, algo, stream)
         self.launches += 1
         return False
+
+    # ---- overlap: buckets leave from inside backward ------------------------------------
+    def _make_hook(self, bi: int):
+        def hook(param):
+            b = self.buckets[bi]
+            b.ready += 1
+            if b.ready > b.hi - b.lo:
+                self._dirty = True       # second backward before a sync: what left early is stale
+            elif b.ready == b.hi - b.lo:
+                self._launch_ready()
+        return hook
+
+    def _launch_ready(self):
+        """Enqueue pack + reduce of every bucket that is complete, strictly in bucket order (all
+        ranks must issue the cross-GPU kernels in the same order), on the side stream, behind
+        everything the current stream has enqueued so far."""
+        main = torch.cuda.current_stream()
+        forked = False
+        while self._next < len(self.buckets):
+            b = self.buckets[self._next]
+            if b.ready < b.hi - b.lo or b.launched:
+                break
+            if not forked:
+                self._side.wait_stream(main)
+                forked = True
+            gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])
+            b.fused_pending = self._pack_and_reduce(b, gs, fuse_oneshot=False, stream=self._side)
+            b.launched = True
+            self._next += 1
+
+    def _finish_overlap(self):
+        """After backward: whatever has not left yet leaves now, then the current stream joins the
+        side stream.  Returns False if the early results cannot be used (a gradient changed after
+        its bucket left) and the caller must run the plain path."""
+        if self._dirty:
+            torch.cuda.current_stream().wait_stream(self._side)
+            self._reset_overlap()
+            return False
+        for b in self.buckets:
+            b.ready = b.hi - b.lo if all(p.grad is not None for p in self.params[b.lo:b.hi]) else b.ready
+        self._launch_ready()
+        if self._next < len(self.buckets):
+            self._grads(self.buckets[self._next])        # raises the reference's error for a missing gradient
+        torch.cuda.current_stream().wait_stream(self._side)
+        return True
+
+    def _reset_overlap(self):
+        for b in self.buckets:
+            b.ready, b.launched, b.fused_pending = 0, False, False
+        self._next = 0
+        self._dirty = False
 
     # ---- strict drop-in: p.grad <- average --------------------------------------------
     def sync(self):
@@ -139,33 +234,53 @@ class GradSync:
         if self.world == 1:
             return            # all_reduce over one rank and a division by 1 change nothing
         _, divisor = self._scales()
+        early = self.overlap and self._finish_overlap()
         for b in self.buckets:
             gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])
-            self._pack_and_reduce(b, gs, fuse_oneshot=False)
+            if not early:
+                self._pack_and_reduce(b, gs, fuse_oneshot=False)
             self.ctx.unpack(b.plan, self.ctx.bucket_ptr(b.result_offset), gs, divisor)
             self.launches += 1
+        if self.overlap:
+            self._reset_overlap()
 
     # ---- fused with the optimizer ---------------------------------------------------------
-    def sync_and_step(self, moms, hyper: dict, first_step: bool, write_grads: bool = True):
-        """Sync fused with torch.optim.SGD.step (codes/task2/model.py:60-62): the
+    def sync_and_step(self, moms, hyper: dict, first_step: bool, write_grads: bool = True, rule="sgd", vels=None):
+        """Sync fused with the optimizer step (codes/task2/model.py:60-62): the
         averaged gradient goes from the bucket straight into the update; p.grad
-        receives it too when write_grads (the state the reference leaves)."""
+        receives it too when write_grads (the state the reference leaves).
+        rule "sgd": torch.optim.SGD with `hyper`; "adam" / "gd": the lab's own optimizers."""
         _, divisor = self._scales()
-        args = sgd_args(first_step=first_step, grad_divisor=divisor, **hyper)
-        has_mom = hyper.get("momentum", 0.0) != 0.0
+        if rule == "sgd":
+            args = sgd_args(first_step=first_step, grad_divisor=divisor, **hyper)
+            has_mom = hyper.get("momentum", 0.0) != 0.0
+        else:
+            args = opt_args(rule, grad_divisor=divisor, **hyper)
+            has_mom = rule == "adam"
+        early = self.overlap and self._finish_overlap()
         for b in self.buckets:
             gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])      # gathered once, used by pack and update
-            fused = self._pack_and_reduce(b, gs, fuse_oneshot=True)
+            fused = False
+            if not early:
+                fused = self._pack_and_reduce(b, gs, fuse_oneshot=(rule == "sgd"))
             ps = [p.data_ptr() for p in self.params[b.lo:b.hi]]
             ms = [m.data_ptr() for m in moms[b.lo:b.hi]] if has_mom else None
             go = gs if write_grads else None
-            if fused:
+            if rule != "sgd":
+                vs = [v.data_ptr() for v in vels[b.lo:b.hi]] if rule == "adam" else None
+                self.ctx.unpack_opt(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, vs, go, args)
+            elif fused:
                 self.ctx.allreduce_sgd(b.plan, b.offset, ps, ms, go, args)
             else:
                 self.ctx.unpack_sgd(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, go, args)
             self.launches += 1
+        if self.overlap:
+            self._reset_overlap()
 
     def close(self):
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
         for b in self.buckets:
             b.plan.close()
         self.buckets = []

@@ -14,7 +14,7 @@ import torch
 from torch.optim.optimizer import Optimizer
 
 from . import _lib
-from .runtime import default_context, sgd_args
+from .runtime import default_context, opt_args, sgd_args
 
 
 class SGD(Optimizer):
@@ -105,3 +105,100 @@ class SGD(Optimizer):
                     self._direct(ctx, [params[i] for i in sel], [bufs[i] for i in sel] if bufs is not None else None,
                                  hyper, first_step=want and hyper["momentum"] != 0)
         return loss
+
+
+# ---------------------------------------------------------------------------------------------
+# The lab's own optimizers (task 1): same constructors, attributes and step()/zero_grad() as
+# codes/task1/pytorch/MyOptimizer.py:3-43, one multi-tensor kernel per step instead of 1 to 9
+# tensor operations per parameter.
+# ---------------------------------------------------------------------------------------------
+class BaseOptimizer:
+    """codes/task1/pytorch/MyOptimizer.py:3-16."""
+    _rule = None
+
+    def __init__(self, params, lr=0.001):
+        self.params = list(params)
+        self.lr = lr
+        self._plans = {}
+        self._engine = None          # set by b200ddp.enable_fused_step
+        self._write_grads = True
+        self.launches = 0
+
+    def step(self):
+        raise NotImplementedError
+
+    def zero_grad(self):
+        for p in self.params:
+            if p.grad is not None:
+                p.grad.detach_()
+                p.grad.zero_()
+
+    def _hyper(self):
+        return dict(lr=self.lr)
+
+    def _states(self, idx):
+        return None, None
+
+    def _step(self):
+        eng = self._engine
+        if eng is not None and eng.pending and eng.world == 1:
+            eng.pending = False
+        if eng is not None and eng.pending:
+            m, v = self._states(range(len(self.params)))
+            before = eng.launches
+            eng.sync_and_step(m, self._hyper(), first_step=False, write_grads=self._write_grads, rule=self._rule, vels=v)
+            self.launches += eng.launches - before
+            eng.pending = False
+            return
+        idx = [i for i, p in enumerate(self.params) if p.grad is not None]     # MyOptimizer.py:22,37
+        if not idx:
+            return
+        ps = [self.params[i] for i in idx]
+        for p in ps:
+            if p.dtype != torch.float32 or not p.is_cuda or not p.is_contiguous() or not p.grad.is_contiguous():
+                raise _lib.B200DDPError("b200ddp optimizers handle contiguous fp32 CUDA parameters and gradients")
+        ctx = default_context()
+        key = tuple(idx)
+        plan = self._plans.get(key)
+        if plan is None:
+            plan = self._plans[key] = ctx.plan([p.numel() for p in ps])
+        m, v = self._states(idx)
+        ctx.opt_step(plan, [p.grad.data_ptr() for p in ps], [p.data_ptr() for p in ps],
+                     [t.data_ptr() for t in m] if m is not None else None,
+                     [t.data_ptr() for t in v] if v is not None else None,
+                     opt_args(self._rule, **self._hyper()))
+        self.launches += 1
+
+
+class GdOptimizer(BaseOptimizer):
+    """codes/task1/pytorch/MyOptimizer.py:18-23: p = p - lr * grad."""
+    _rule = "gd"
+
+    @torch.no_grad()
+    def step(self):
+        self._step()
+
+
+class AdamOptimizer(BaseOptimizer):
+    """codes/task1/pytorch/MyOptimizer.py:25-43: Adam without bias correction, state in
+    `momentums` / `velocities` (zeros at construction), every tensor operation of the reference's
+    expression rounded on its own."""
+    _rule = "adam"
+
+    def __init__(self, params, lr=0.001, b1=0.9, b2=0.999, epsilon=1e-8):
+        super().__init__(params, lr)
+        self.beta1 = b1
+        self.beta2 = b2
+        self.epsilon = epsilon
+        self.momentums = [torch.zeros_like(p, memory_format=torch.contiguous_format) for p in self.params]
+        self.velocities = [torch.zeros_like(p, memory_format=torch.contiguous_format) for p in self.params]
+
+    def _hyper(self):
+        return dict(lr=self.lr, beta1=self.beta1, beta2=self.beta2, eps=self.epsilon)
+
+    def _states(self, idx):
+        return [self.momentums[i] for i in idx], [self.velocities[i] for i in idx]
+
+    @torch.no_grad()
+    def step(self):
+        self._step()

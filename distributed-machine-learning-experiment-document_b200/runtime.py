@@ -98,7 +98,10 @@ class Context:
         self.has_multicast = False
         self.symmetric_error = None
         self._symmetric = None                 # (tensor, handle) of adopted torch symmetric memory
+        self._group = None                     # process group the peers were connected over (None: default group)
+        self._ipc = False                      # peers opened over CUDA IPC (teardown is collective then)
         self._plans = weakref.WeakSet()
+        self._bcast_plans = {}                 # flat-broadcast plans, by tensor-size list
 
     # ---- set-up --------------------------------------------------------------
     def connect(self, group=None, nccl=True, p2p=True):
@@ -106,6 +109,7 @@ class Context:
         the library's own NCCL communicator."""
         if self.world == 1:
             return self
+        self._group = group
         if p2p and not self.has_peers:
             mine = ctypes.create_string_buffer(_lib.IPC_BYTES)
             check(_lib.lib().b200ddp_ipc_export(self.handle, mine), "ipc_export")
@@ -114,6 +118,7 @@ class Context:
             blob = ctypes.create_string_buffer(b"".join(handles), _lib.IPC_BYTES * self.world)
             check(_lib.lib().b200ddp_ipc_open_peers(self.handle, blob), "ipc_open_peers")
             self.has_peers = True
+            self._ipc = True
         if nccl and not self.has_nccl:
             uid = ctypes.create_string_buffer(_lib.NCCL_UID_BYTES)
             if self.rank == 0:
@@ -165,7 +170,8 @@ class Context:
             return
         check(_lib.lib().b200ddp_adopt_symmetric(self.handle, ptr_array(ptrs), c_void_p(mc) if mc else None, nbytes),
               "adopt_symmetric")
-        dist.barrier(group=group)       # everyone zeroed and adopted before anyone packs
+        dist.barrier(group=group)       # everyone zeroed, adopted and closed its mappings of the old areas ...
+        check(_lib.lib().b200ddp_free_retired(self.handle), "free_retired")     # ... so the old area can go
         self._symmetric = (tensor, handle)
         self.staging_ptr = tensor.data_ptr()
         self.has_multicast = bool(mc)
@@ -200,16 +206,33 @@ class Context:
         self.has_peers = True
         return self
 
-    def close(self):
+    def close(self, collective=True):
+        """Frees the context.  With peers opened over CUDA IPC the teardown is collective: every rank
+        closes its mappings of the others' memory, all ranks meet at a barrier, then each frees its
+        own (an exported area must outlive its importers).  collective=False (garbage collection,
+        interpreter exit) skips the barrier."""
         if getattr(self, "handle", None):
             for pl in list(self._plans):
                 pl.close()
+            if collective and self.world > 1 and self._ipc and self._group_alive():
+                try:
+                    check(_lib.lib().b200ddp_close_peers(self.handle), "close_peers")
+                    dist.barrier(group=self._group)
+                except Exception:
+                    pass
             _lib.lib().b200ddp_destroy(self.handle)
             self.handle = None
+            self._symmetric = None
+
+    def _group_alive(self):
+        try:
+            return dist.is_available() and dist.is_initialized() and (self._group is None or dist.get_rank(self._group) >= 0)
+        except Exception:
+            return False
 
     def __del__(self):
         try:
-            self.close()
+            self.close(collective=False)
         except Exception:
             pass
 
@@ -242,6 +265,10 @@ class Context:
         check(_lib.lib().b200ddp_allreduce(self.handle, int(offset_bytes), int(nelem), dtype_code(dtype), a,
                                            _stream_handle(stream), byref(res)), "allreduce")
         return int(res.value)
+
+    def barrier(self, stream=None):
+        """Device-side barrier over all ranks on `stream` (no host synchronisation)."""
+        check(_lib.lib().b200ddp_barrier(self.handle, _stream_handle(stream)), "barrier")
 
     def allreduce_pick(self, nelem: int, dtype) -> int:
         return int(_lib.lib().b200ddp_allreduce_pick(self.handle, int(nelem), dtype_code(dtype)))

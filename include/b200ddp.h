@@ -103,6 +103,15 @@ int b200ddp_set_peers_direct(b200ddp_ctx *ctx, void *const *staging_ptrs, void *
  * caller, which must keep the memory alive until b200ddp_destroy.  Collective in effect: every
  * rank must adopt, or none. */
 int b200ddp_adopt_symmetric(b200ddp_ctx *ctx, void *const *peer_ptrs, void *mc_ptr, size_t bytes);
+/* Memory exported over CUDA IPC must not be freed while a peer still has it mapped, so giving it up
+ * takes two steps with a cross-rank barrier (the caller's: torch.distributed.barrier) between them:
+ *   adopt:    b200ddp_adopt_symmetric (closes this rank's mappings of the peers' old staging and retires
+ *             its own) | barrier | b200ddp_free_retired (frees the retired area)
+ *   teardown: b200ddp_close_peers (synchronises the device, closes every imported mapping) | barrier |
+ *             b200ddp_destroy.
+ * b200ddp_destroy alone still closes and frees everything; the barrier is what makes the order safe. */
+int b200ddp_free_retired(b200ddp_ctx *ctx);
+int b200ddp_close_peers(b200ddp_ctx *ctx);
 
 /* ---- plan: bucket layout of a list of T fp32 tensors ------------------------
  * Tensor t occupies bucket elements [offset[t], offset[t] + numel[t]); offsets
@@ -136,6 +145,11 @@ int b200ddp_pack_scale(b200ddp_ctx *ctx, b200ddp_plan *plan, const void *const *
  * so AUTO never picks NCCL for a bf16 bucket. */
 int b200ddp_allreduce(b200ddp_ctx *ctx, size_t offset_bytes, int64_t nelem, int dtype, int algo,
                       b200ddp_stream stream, size_t *result_offset_bytes);
+/* Device-side barrier over all ranks, enqueued on `stream` (one tiny kernel, no host synchronisation):
+ * what each rank enqueued before it is visible to what every rank enqueues after it.  Collective.
+ * Stands in for the implicit ordering of the per-parameter `dist.broadcast` calls of init_parameters,
+ * codes/task2/dist_utils.py:33-37, in the flat broadcast (rank 0 packs | barrier | peers read). */
+int b200ddp_barrier(b200ddp_ctx *ctx, b200ddp_stream stream);
 /* which algorithm AUTO resolves to for this size (host-only, no device work) */
 int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype);
 

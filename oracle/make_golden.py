@@ -17,6 +17,8 @@ What is frozen:
   * ddp_grid_<variant>_ws<N>.npz - reference sync + torch SGD on a ragged tensor
     set with injected gradients (oracle/synth.py), several SGD flag sets.
   * sampler_*.npz - torch DistributedSampler (codes/task2/model.py:124) outputs.
+  * opt_{gd,adam,adam_b}.npz - the lab's own GdOptimizer / AdamOptimizer
+    (codes/task1/pytorch/MyOptimizer.py:18-43, imported by path) on injected gradients.
   * bf16_hook_ws{2,8}.npz - torch's bf16_compress_hook under DDP/gloo on injected gradients
     (the semantics bf16 buckets are compared with; the reference itself is fp32 only).
 
@@ -281,8 +283,73 @@ def make_sampler():
     print("sampler ok")
 
 
+def make_lab_optimizers(steps=4):
+    """The lab's own GdOptimizer / AdamOptimizer (codes/task1/pytorch/MyOptimizer.py), imported by path
+    and run on the ragged tensor set with injected gradients; the numpy restatements must agree bit
+    for bit.  Steps 0..steps-1 use dense gradients; one tensor also sees zeros (sqrt(0) + eps path)."""
+    from oracle import ref_ddp, synth
+    ref = _load("ref_t1_myoptimizer", f"{REF}/task1/pytorch/MyOptimizer.py")
+    numels = synth.RAGGED_NUMELS
+
+    def grad(n, s, t):
+        g = synth.dense_grad(n, 0, s, t)
+        if t == 11:
+            g[::3] = 0.0
+        return g
+
+    for name, ctor, hp in (("gd", ref.GdOptimizer, dict(lr=0.05)),
+                           ("adam", ref.AdamOptimizer, dict(lr=0.002, b1=0.9, b2=0.999, epsilon=1e-8)),
+                           ("adam_b", ref.AdamOptimizer, dict(lr=0.01, b1=0.8, b2=0.95, epsilon=1e-6))):
+        params = [torch.nn.Parameter(torch.from_numpy(synth.init_param(n, t))) for t, n in enumerate(numels)]
+        opt = ctor(params, **hp)
+        kw = dict(lr=hp["lr"]) if name == "gd" else dict(lr=hp["lr"], beta1=hp["b1"], beta2=hp["b2"], eps=hp["epsilon"])
+        p_np = [synth.init_param(n, t) for t, n in enumerate(numels)]
+        m_np = [np.zeros(n, np.float32) for n in numels]
+        v_np = [np.zeros(n, np.float32) for n in numels]
+        p_t = [torch.from_numpy(a.copy()) for a in p_np]
+        m_t = [torch.zeros(n) for n in numels]
+        v_t = [torch.zeros(n) for n in numels]
+        for s in range(steps):
+            for t, p in enumerate(params):
+                p.grad = torch.from_numpy(grad(p.numel(), s, t))
+            opt.step()
+            for t, n in enumerate(numels):
+                g = grad(n, s, t)
+                if name == "gd":
+                    p_np[t] = ref_ddp.gd_step_numpy(p_np[t], g, **kw)
+                    p_t[t] = ref_ddp.gd_step_torch(p_t[t], torch.from_numpy(g), **kw)
+                else:
+                    p_np[t], m_np[t], v_np[t] = ref_ddp.adam_step_numpy(p_np[t], g, m_np[t], v_np[t], **kw)
+                    p_t[t], m_t[t], v_t[t] = ref_ddp.adam_step_torch(p_t[t], torch.from_numpy(g), m_t[t], v_t[t], **kw)
+        out = {"p": _flat(params), "steps": np.int64(steps), "hp": np.asarray(list(hp.values()), np.float64)}
+        assert np.array_equal(out["p"], _flat(p_t)), f"{name}: torch restatement differs from the reference"
+
+        def close(a, b):
+            return np.max(np.abs(a - b)) <= 1e-6 * np.max(np.abs(a))
+        if name == "gd":
+            assert np.array_equal(out["p"], np.concatenate(p_np)), "gd: numpy restatement differs from the reference"
+        else:
+            out["m"], out["v"] = _flat(opt.momentums), _flat(opt.velocities)
+            assert np.array_equal(out["m"], _flat(m_t)) and np.array_equal(out["v"], _flat(v_t))
+            assert np.array_equal(out["m"], np.concatenate(m_np)) and np.array_equal(out["v"], np.concatenate(v_np))
+            assert close(out["p"], np.concatenate(p_np)), "adam: numpy restatement is off by more than 1e-6"
+        np.savez_compressed(os.path.join(OUT, f"opt_{name}.npz"), **out)
+        print("lab optimizer", name, "ok")
+
+
+def lab_optimizer_grad(n, s, t):
+    """The gradients make_lab_optimizers injects (shared with the tests)."""
+    from oracle import synth
+    g = synth.dense_grad(n, 0, s, t)
+    if t == 11:
+        g[::3] = 0.0
+    return g
+
+
 def main():
     os.makedirs(OUT, exist_ok=True)
+    if "--lab-optimizers-only" in sys.argv:
+        return make_lab_optimizers()
     make_sampler()
     make_labnet(2)
     make_labnet(4)
@@ -294,6 +361,7 @@ def main():
     make_grid("A", 8, kind="dense")
     make_bf16_hook(2)
     make_bf16_hook(8)
+    make_lab_optimizers()
 
 
 if __name__ == "__main__":

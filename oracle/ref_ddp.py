@@ -143,6 +143,53 @@ def sgd_step_numpy(p, g, buf, *, lr, momentum=0.0, dampening=0.0,
 
 
 # --------------------------------------------------------------------------
+# the lab's own optimizers, codes/task1/pytorch/MyOptimizer.py:18-43, op by op as torch
+# evaluates the expressions on fp32 tensors (each tensor operation rounds once):
+#   GD    p = p - lr * g                                             (:23)
+#   Adam  m = b1 * m + (1 - b1) * g                                  (:39)
+#         v = b2 * v + (1 - b2) * g**2                               (:41)
+#         p = p - (lr / (sqrt(v) + eps)) * m                         (:42-43)
+# `(1 - b1)` is evaluated by Python in double before the product casts it to fp32;
+# `lr / tensor` is Tensor.__rtruediv__ = tensor.reciprocal() * lr.
+# Pinned against the reference classes themselves in make_golden.py (opt_*.npz):
+#   * adam_step_torch is the reference's three statements verbatim on torch tensors; on the CPU it
+#     reproduces the reference class bit for bit (same ATen kernels), and on a CUDA device it is the
+#     reference's arithmetic on the GPU (the GPU tests run it there).
+#   * the numpy functions use IEEE sqrt / division, which is what ATen's CUDA kernels compute.
+#     ATen's CPU sqrt (MKL VML) is NOT correctly rounded (0.65 % of fp32 inputs differ by one ulp,
+#     measured in this container), so against the CPU goldens they are held to rel <= 1e-6 on m, v
+#     and p rather than to bit equality; GD has no sqrt and is bit-exact everywhere.
+# --------------------------------------------------------------------------
+def adam_step_torch(p, g, m, v, *, lr, beta1=0.9, beta2=0.999, eps=1e-8):
+    """codes/task1/pytorch/MyOptimizer.py:39-43 on torch tensors of any device; returns (p, m, v)."""
+    m = beta1 * m + (1 - beta1) * g
+    v = beta2 * v + (1 - beta2) * g ** 2
+    p = p - (lr / (v.sqrt() + eps)) * m
+    return p, m, v
+
+
+def gd_step_torch(p, g, *, lr):
+    """codes/task1/pytorch/MyOptimizer.py:23."""
+    return p - lr * g
+
+
+def gd_step_numpy(p, g, *, lr):
+    p, g = np.asarray(p, np.float32), np.asarray(g, np.float32)
+    return (p - (np.float32(lr) * g).astype(np.float32)).astype(np.float32)
+
+
+def adam_step_numpy(p, g, m, v, *, lr, beta1=0.9, beta2=0.999, eps=1e-8):
+    """Returns (new_p, new_m, new_v); m and v start as zeros (MyOptimizer.py:32-33)."""
+    f = np.float32
+    p, g, m, v = (np.asarray(a, f) for a in (p, g, m, v))
+    m = ((f(beta1) * m).astype(f) + (f(1 - beta1) * g).astype(f)).astype(f)
+    v = ((f(beta2) * v).astype(f) + (f(1 - beta2) * (g * g).astype(f)).astype(f)).astype(f)
+    den = (np.sqrt(v).astype(f) + f(eps)).astype(f)
+    step = (((f(1) / den).astype(f) * f(lr)).astype(f) * m).astype(f)
+    return (p - step).astype(f), m, v
+
+
+# --------------------------------------------------------------------------
 # the lab CNN: same layers, shapes and parameter order as `Net` at
 # codes/task2/model.py:13-37 (51,902 parameters in 8 tensors).
 # --------------------------------------------------------------------------

@@ -51,10 +51,10 @@ class FakeCtx:
         nbytes = nelem * (2 if dtype == _lib.BF16 else 4)
         return _lib.ALGO_ONESHOT if nbytes <= self.oneshot_max else _lib.ALGO_TWOSHOT
 
-    def pack_scale(self, plan, ptrs, bucket, scale):
+    def pack_scale(self, plan, ptrs, bucket, scale, stream=None):
         self.calls.append(("pack", len(list(ptrs)), bucket - self.staging_ptr, scale))
 
-    def allreduce(self, off, nelem, dtype, algo):
+    def allreduce(self, off, nelem, dtype, algo, stream=None):
         self.calls.append(("allreduce", off, nelem, algo))
         return off + (self.staging_bytes if algo == _lib.ALGO_ONESHOT else 0)     # one-shot result is out of place
 
@@ -143,3 +143,21 @@ def test_missing_gradient_raises_like_the_reference():
     ps[1].grad = None
     with pytest.raises(AttributeError):
         GradSync(ps, ctx).sync()
+
+
+def test_reverse_split_puts_the_tail_of_the_list_first():
+    """Overlap mode cuts buckets from the LAST parameter backwards (the order backward produces
+    gradients in): bucket 0 is the tail, the last bucket holds parameter 0, every tensor is in
+    exactly one bucket, and each bucket keeps list order inside."""
+    from b200ddp.engine import split_buckets_reverse
+    numels = [9408, 64, 64, 36864, 64, 64, 2_359_296, 512, 512, 5120, 10]
+    layout = split_buckets_reverse(numels, 4, 4 << 20, 64 << 20)
+    assert layout[0][1] == len(numels) and layout[-1][0] == 0
+    covered = []
+    for lo, hi, off, elems in layout:
+        assert lo < hi and elems == sum(padded_numel(n) for n in numels[lo:hi]) and off % 256 == 0
+        covered = list(range(lo, hi)) + covered
+    assert covered == list(range(len(numels)))
+    # offsets do not overlap
+    spans = sorted((off, off + elems * 4) for _, _, off, elems in layout)
+    assert all(a[1] <= b[0] for a, b in zip(spans, spans[1:]))

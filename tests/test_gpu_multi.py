@@ -348,3 +348,238 @@ def test_resnet18_sized_buckets_all_algorithms(ws):
 
 def test_ddp_comm_hook_two_ranks():
     _run(2, _ddp_hook)
+
+
+# ------------------------------------------------------------------ round 2: overlap, sub-groups, odd worlds, lab optimizers
+def _overlap_equals_plain(rank, ws, graphed):
+    """Buckets that leave from inside backward (reverse-order buckets, side stream) must give the bits
+    the plain after-backward sync gives: same sums, same update, eager and replayed from a CUDA graph."""
+    import b200ddp
+    from oracle import ref_ddp
+    outs = []
+    for overlap in (False, True):
+        b200ddp.configure(algo="auto", overlap=overlap, bucket_cap_bytes=(1 << 20) if overlap else 0)
+        torch.manual_seed(5)
+        # linear layers: their backward is run-to-run deterministic, and four of them give several buckets
+        model = torch.nn.Sequential(torch.nn.Flatten(), torch.nn.Linear(784, 512), torch.nn.ReLU(),
+                                    torch.nn.Linear(512, 512), torch.nn.ReLU(), torch.nn.Linear(512, 256),
+                                    torch.nn.ReLU(), torch.nn.Linear(256, 10)).cuda()
+        b200ddp.init_parameters(model)
+        opt = b200ddp.SGD(model.parameters(), lr=0.01, momentum=0.9)
+        b200ddp.enable_fused_step(model, opt)
+        loss_fn = torch.nn.CrossEntropyLoss()
+        step = b200ddp.GraphedTrainStep(model, loss_fn, opt, eager_steps=2) if graphed else None
+        for s in range(7):
+            x, y = ref_ddp.synthetic_batch(rank, s, 32, (1, 28, 28), 10)
+            x, y = x.cuda(), y.cuda()
+            if graphed:
+                step(x, y)
+            else:
+                loss = loss_fn(model(x), y)
+                opt.zero_grad()
+                loss.backward()
+                b200ddp.allreduce_average_gradients(model)
+                opt.step()
+        torch.cuda.synchronize()
+        eng = b200ddp.dist_utils.engine_for(model)
+        if overlap:
+            assert eng.overlap and len(eng.buckets) >= 3 and eng.buckets[0].hi == len(eng.params)
+        if graphed:
+            assert step.capture_error is None and step.graph is not None, step.capture_error
+        outs.append(torch.cat([p.detach().flatten() for p in model.parameters()] +
+                              [p.grad.flatten() for p in model.parameters()]))
+    b200ddp.configure(overlap=False, bucket_cap_bytes=0)
+    assert torch.equal(outs[0], outs[1]), "overlapped buckets changed the result"
+    mine = outs[1].clone()
+    torch.distributed.broadcast(mine, 0)
+    assert torch.equal(mine, outs[1]), "ranks diverged"
+
+
+def _overlap_strict_and_stale(rank, ws):
+    """Strict mode with overlap (p.grad <- mean after the call), and the fallback when gradients are
+    accumulated twice before the sync (what left early is stale and must not be used)."""
+    import b200ddp
+    b200ddp.configure(algo="auto", overlap=True, bucket_cap_bytes=1 << 20)
+    torch.manual_seed(1)
+    model = torch.nn.Sequential(torch.nn.Linear(600, 600), torch.nn.ReLU(), torch.nn.Linear(600, 600),
+                                torch.nn.ReLU(), torch.nn.Linear(600, 10)).cuda()
+    b200ddp.init_parameters(model)
+    gen = torch.Generator(device="cuda").manual_seed(9 + rank)
+    for accumulate in (1, 2, 1):
+        model.zero_grad(set_to_none=True)
+        for _ in range(accumulate):
+            x = torch.randn(16, 600, device="cuda", generator=gen)
+            model(x).square().mean().backward()
+        local = [p.grad.clone() for p in model.parameters()]
+        b200ddp.allreduce_average_gradients(model)
+        for p, g in zip(model.parameters(), local):
+            ref = g.clone()
+            torch.distributed.all_reduce(ref)
+            ref /= ws
+            assert (p.grad - ref).abs().max() <= 1e-5 * ref.abs().max().clamp_min(1e-30)
+            if ws == 2:
+                assert torch.equal(p.grad, ref)
+    b200ddp.configure(overlap=False, bucket_cap_bytes=0)
+
+
+def _subgroups(rank, ws):
+    """replicas of a pipeline stage sync over their own sub-group.  Ranks are split
+    into `ws // 2` replicas x 2 stages (stage = rank % 2); each stage's gradients are averaged over the ranks
+    holding that stage, on contexts connected over that sub-group."""
+    import b200ddp
+    from b200ddp.engine import GradSync
+    stages = 2
+    replicas = ws // stages
+    groups = [torch.distributed.new_group([r for r in range(ws) if r % stages == s]) for s in range(stages)]
+    stage = rank % stages
+    grp = groups[stage]
+    ctx = b200ddp.Context(rank // stages, replicas, torch.cuda.current_device(), staging_bytes=16 << 20)
+    ctx.connect(group=grp)
+    numels = (150, 6, 2400, 16) if stage == 0 else (48000, 120, 1200, 10)      # the task4 split, codes/task4/model.py:18-46
+    params = [torch.nn.Parameter(torch.full((n,), float(stage), device="cuda")) for n in numels]
+    gen = torch.Generator(device="cuda").manual_seed(30 + rank)
+    for algo in ("twoshot", "oneshot", "nccl", "auto"):
+        eng = GradSync(params, ctx, algo=algo)
+        local = [torch.randn(n, device="cuda", generator=gen) * 1e-2 for n in numels]
+        for p, g in zip(params, local):
+            p.grad = g.clone()
+        eng.sync()
+        for p, g in zip(params, local):
+            parts = [torch.empty_like(g) for _ in range(replicas)]
+            torch.distributed.all_gather(parts, g, group=grp)
+            acc = parts[0].clone()
+            for t in parts[1:]:
+                acc += t
+            acc /= replicas
+            if algo != "nccl":
+                assert torch.equal(p.grad, acc), (algo, "sub-group mean differs")
+            else:
+                assert (p.grad - acc).abs().max() <= 1e-5 * acc.abs().max()
+        eng.close()
+    # the flat broadcast inside the sub-group: replica 0 of each stage is the source
+    src = [torch.full((n,), 100.0 * stage + rank, device="cuda") for n in numels]
+    b200ddp.broadcast_from_rank0(src, ctx)
+    assert all(float(t[0]) == 100.0 * stage + stage for t in src)          # global rank of replica 0 of this stage = stage
+    torch.cuda.synchronize()
+    torch.distributed.barrier()
+    ctx.close()
+
+
+def _odd_world(rank, ws):
+    """Three ranks: the sum in rank order, then the division as torch rounds it on CUDA - bit for bit
+    against torch's own arithmetic on gathered gradients (codes/task2/dist_utils.py:41-42 run on the GPU)."""
+    import b200ddp
+    from b200ddp.engine import GradSync
+    numels = (1000, 4099, 33, 70_000)
+    params = [torch.nn.Parameter(torch.zeros(n, device="cuda")) for n in numels]
+    gen = torch.Generator(device="cuda").manual_seed(70 + rank)
+    for algo in ("twoshot", "oneshot", "auto"):
+        local = [torch.randn(n, device="cuda", generator=gen) * 1e-2 for n in numels]
+        want = []
+        for g in local:
+            parts = [torch.empty_like(g) for _ in range(ws)]
+            torch.distributed.all_gather(parts, g)
+            acc = parts[0].clone()
+            for t in parts[1:]:
+                acc += t
+            acc /= ws
+            want.append(acc)
+        eng = GradSync(params, b200ddp.default_context(), algo=algo)
+        for p, g in zip(params, local):
+            p.grad = g.clone()
+        eng.sync()
+        assert all(torch.equal(p.grad, w) for p, w in zip(params, want)), algo
+        # fused with the update: the division happens inside K3
+        with torch.no_grad():
+            for p in params:
+                p.fill_(0.5)
+        for p, g in zip(params, local):
+            p.grad = g.clone()
+        moms = [torch.empty_like(p) for p in params]
+        eng.sync_and_step(moms, dict(lr=0.1, momentum=0.9), first_step=True)
+        for p, m, w in zip(params, moms, want):
+            assert torch.equal(p.grad, w) and torch.equal(m, w)
+            # p + (-lr) * g as ONE fused multiply-add (torch/optim/sgd.py:380), formed in fp64
+            fma = (0.5 + w.double() * torch.tensor(-0.1, dtype=torch.float32).double()).float()
+            assert torch.equal(p.detach(), fma)
+        eng.close()
+
+
+def _lab_optimizers_fused(rank, ws):
+    """The lab's Adam / GD fused with the sync (pack -> reduce -> unpack + rule) against the reference's
+    statements run by torch on the averaged gradients."""
+    import b200ddp
+    from oracle import ref_ddp
+    for cls in ("gd", "adam"):
+        torch.manual_seed(3)
+        model = torch.nn.Sequential(torch.nn.Linear(300, 200), torch.nn.ReLU(), torch.nn.Linear(200, 10)).cuda()
+        b200ddp.configure(algo="auto")
+        b200ddp.init_parameters(model)
+        params = list(model.parameters())
+        opt = b200ddp.GdOptimizer(params, lr=0.05) if cls == "gd" else b200ddp.AdamOptimizer(params, lr=0.002)
+        b200ddp.enable_fused_step(model, opt)
+        pt = [p.detach().clone() for p in params]
+        mt, vt = [torch.zeros_like(p) for p in params], [torch.zeros_like(p) for p in params]
+        gen = torch.Generator(device="cuda").manual_seed(11 + rank)
+        for s in range(3):
+            for p in params:
+                p.grad = torch.randn(p.shape, device="cuda", generator=gen) * 1e-2
+            avg = []
+            for p in params:
+                parts = [torch.empty_like(p.grad) for _ in range(ws)]
+                torch.distributed.all_gather(parts, p.grad)
+                acc = parts[0].clone()
+                for t in parts[1:]:
+                    acc += t
+                avg.append(acc / ws)
+            b200ddp.allreduce_average_gradients(model)
+            opt.step()
+            for i in range(len(params)):
+                if cls == "gd":
+                    pt[i] = ref_ddp.gd_step_torch(pt[i], avg[i], lr=0.05)
+                else:
+                    pt[i], mt[i], vt[i] = ref_ddp.adam_step_torch(pt[i], avg[i], mt[i], vt[i], lr=0.002)
+            for p, a, w in zip(params, avg, pt):
+                assert torch.equal(p.grad, a) if ws == 2 else (p.grad - a).abs().max() <= 1e-5 * a.abs().max()
+                if ws == 2:
+                    assert torch.equal(p.detach(), w), cls
+                else:
+                    assert (p.detach() - w).abs().max() <= 1e-5 * w.abs().max()
+
+
+@pytest.mark.parametrize("graphed", [False, True])
+def test_overlap_equals_plain_two_ranks(graphed):
+    _run(2, _overlap_equals_plain, graphed)
+
+
+def test_overlap_equals_plain_eight_ranks_graphed():
+    _run(8, _overlap_equals_plain, True)
+
+
+def test_overlap_strict_and_stale_two_ranks():
+    _run(2, _overlap_strict_and_stale)
+
+
+def test_subgroup_contexts_four_ranks():
+    _run(4, _subgroups)
+
+
+def test_subgroup_contexts_eight_ranks():
+    _run(8, _subgroups)
+
+
+def test_three_ranks_sum_then_divide_bit_exact():
+    _run(3, _odd_world)
+
+
+def test_lab_optimizers_fused_two_ranks():
+    _run(2, _lab_optimizers_fused)
+
+
+@pytest.mark.parametrize("ws", [4, 8])
+def test_ddp_comm_hook_more_ranks(ws):
+    _run(ws, _ddp_hook)
+
+
+def test_next_rows_four_ranks():
+    _run(4, _next_rows)

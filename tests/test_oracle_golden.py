@@ -172,3 +172,36 @@ def test_bf16_wire_oracle_against_torch_hook_golden(golden_dir, ws):
         [torch.from_numpy(synth.dense_grad(n, r, 0, t)) for r in range(ws)]).numpy()
         for t, n in enumerate(synth.RAGGED_NUMELS)])
     assert np.max(np.abs(fp32 - g["avg"])) <= 2e-2 * np.max(np.abs(fp32))
+
+
+# ------------------------------------------------------------------ the lab's own optimizers (task 1)
+@pytest.mark.parametrize("name", ["gd", "adam", "adam_b"])
+def test_lab_optimizer_restatements_against_reference_golden(golden_dir, name):
+    """opt_*.npz were produced by the reference's GdOptimizer / AdamOptimizer classes
+    (codes/task1/pytorch/MyOptimizer.py) imported by path.  The torch restatement reproduces them bit
+    for bit on the CPU; the numpy (IEEE sqrt) restatement is bit-exact for GD and for Adam's m and v,
+    and within 1e-6 on Adam's p because ATen's CPU sqrt is not correctly rounded."""
+    from oracle.make_golden import lab_optimizer_grad
+    g = _load(golden_dir, f"opt_{name}.npz")
+    numels, steps, hp = synth.RAGGED_NUMELS, int(g["steps"]), list(g["hp"])
+    kw = dict(lr=hp[0]) if name == "gd" else dict(lr=hp[0], beta1=hp[1], beta2=hp[2], eps=hp[3])
+    p_np = [synth.init_param(n, t) for t, n in enumerate(numels)]
+    m_np = [np.zeros(n, np.float32) for n in numels]
+    v_np = [np.zeros(n, np.float32) for n in numels]
+    p_t = [torch.from_numpy(a.copy()) for a in p_np]
+    m_t, v_t = [torch.zeros(n) for n in numels], [torch.zeros(n) for n in numels]
+    for s in range(steps):
+        for t, n in enumerate(numels):
+            gr = lab_optimizer_grad(n, s, t)
+            if name == "gd":
+                p_np[t] = ref_ddp.gd_step_numpy(p_np[t], gr, **kw)
+                p_t[t] = ref_ddp.gd_step_torch(p_t[t], torch.from_numpy(gr), **kw)
+            else:
+                p_np[t], m_np[t], v_np[t] = ref_ddp.adam_step_numpy(p_np[t], gr, m_np[t], v_np[t], **kw)
+                p_t[t], m_t[t], v_t[t] = ref_ddp.adam_step_torch(p_t[t], torch.from_numpy(gr), m_t[t], v_t[t], **kw)
+    assert np.array_equal(g["p"], np.concatenate([t.numpy() for t in p_t]))
+    if name == "gd":
+        assert np.array_equal(g["p"], np.concatenate(p_np))
+    else:
+        assert np.array_equal(g["m"], np.concatenate(m_np)) and np.array_equal(g["v"], np.concatenate(v_np))
+        assert np.max(np.abs(g["p"] - np.concatenate(p_np))) <= 1e-6 * np.max(np.abs(g["p"]))
