@@ -34,6 +34,7 @@ MODELS = {
     "labnet": ("labnet", 32, 0.01),        # configs[0]: codes/task2/model.py:126,131
     "resnet18": ("resnet18", 128, 0.001),  # configs[1]: codes/task3/model.py:118
     "resnet50": ("resnet50", 256, 0.001),  # configs[2]
+    "task4": ("task4", 32, 0.01),          # configs[3]: codes/task4/model.py:118,126 - two-stage split, replicated
 }
 METRIC = "train samples/sec"
 UNIT = "samples/s"
@@ -78,7 +79,7 @@ def env_int(name, default):
 def build_model(name):
     import torch
     torch.manual_seed(0)             # every rank builds identical weights and BN buffers
-    if name == "labnet":
+    if name in ("labnet", "task4"):  # task4's two stages are this model cut after the second pooling layer
         import torch.nn as nn
 
         class LabCNN(nn.Module):     # layer shapes of `Net`, codes/task2/model.py:13-37
@@ -203,7 +204,7 @@ def _cpu_worker(rank, world, port, model_name, batch, lr, steps, warmup, threads
     if world > 1:
         ref_ddp.dist_init(world, rank, "127.0.0.1", str(port))
     model, chw, classes = build_model(model_name)
-    opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=0.9)
+    opt = torch.optim.SGD(model.parameters(), lr=lr, momentum=0.0 if model_name == "task4" else 0.9)
     loss_fn = torch.nn.CrossEntropyLoss()
     model.train()
     ref_ddp.init_parameters(model)
@@ -296,7 +297,9 @@ def reference_arm(args):
         return 0                     # rank 0 alone runs the N-process gloo job on the host cores
     name, batch, lr = MODELS[args.model]
     batch = args.batch or batch
-    world = args.gpus
+    # task4: the reference runs ONE copy of the split model on CPU RPC workers; its data-parallel counterpart
+    # on the host cores is R = N / 2 gloo ranks of the whole model
+    world = max(1, args.gpus // 2) if args.model == "task4" else args.gpus
     probe_batch = min(batch, 32)
     dt, cores, threads = run_cpu(world, name, probe_batch, lr, 1, 1)
     per_sample = dt / probe_batch
@@ -308,7 +311,7 @@ def reference_arm(args):
     value = world * b * args.steps / dt
     sample = (f"{args.steps} steps x {b} samples/rank x {world} gloo rank(s), {threads} thread(s)/rank of {cores} cores"
               f" (full batch is {batch}/rank)")
-    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+    line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": workload_config(args.model, batch, world),
@@ -320,7 +323,8 @@ def reference_arm(args):
     return 0
 
 
-PARAMS = {"labnet": (51902, 8), "resnet18": (11181642, 62), "resnet50": (25557032, 161)}
+PARAMS = {"labnet": (51902, 8), "resnet18": (11181642, 62), "resnet50": (25557032, 161),
+          "task4": (51902, 8)}
 
 
 def workload_config(model, batch, world):
@@ -329,7 +333,9 @@ def workload_config(model, batch, world):
     P, T = PARAMS[model]
     return {"workload": {"labnet": "task2 lab CNN on MNIST-shaped synthetic data (1x28x28)",
                          "resnet18": "task3 DDP loop: ResNet-18 (10 classes) on CIFAR-10-shaped synthetic data (3x32x32)",
-                         "resnet50": "ResNet-50 on ImageNet-shaped synthetic data (3x224x224)"}[model],
+                         "resnet50": "ResNet-50 on ImageNet-shaped synthetic data (3x224x224)",
+                         "task4": "task4 two-stage split of the lab CNN (conv stage | fc stage), micro-batched, replicated "
+                                  "data-parallel, MNIST-shaped synthetic data (1x28x28)"}[model],
             "batch_per_rank": batch, "global_batch": batch * world, "optimizer": "SGD momentum 0.9",
             "parallelism": f"dp{world}", "params": P, "tensors": T,
             "l2": "inputs larger than L2: the step's working set (params + momentum + grads = %.0f MB, plus "
@@ -627,6 +633,82 @@ def torch_gpu_baseline(torch, dist, b200ddp, name, lr, world, dev, dev_batches, 
     return out
 
 
+def task4_arm(args):
+    """configs[3]: R = N / 2 replicas of the two-stage pipeline, each stage's gradients averaged over its
+    R-rank sub-group on the B200 path (b200ddp.TwoStageReplica).  A step = one batch of 32 per replica in
+    4 micro-batches: forward on both stages, backward, sub-group sync fused with the plain-SGD update."""
+    import torch
+    import torch.distributed as dist
+
+    import b200ddp
+
+    world, rank, local = env_int("WORLD_SIZE", 1), env_int("RANK", 0), env_int("LOCAL_RANK", 0)
+    if world < 2 or world % 2 or world != args.gpus:
+        raise SystemExit("--model task4 needs an even number of GPUs >= 2 (torch.distributed.run, one rank per GPU)")
+    os.environ.setdefault("NCCL_DEBUG", "NONE")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    _, batch, lr = MODELS["task4"]
+    batch = args.batch or batch
+    rep = b200ddp.TwoStageReplica(lr=lr, microbatches=4, seed=0, algo=args.algo)
+    host = make_batches(rep.replica, 8, batch, (1, 28, 28), 10, pin=True)
+    devb = [(x.to(dev), y.to(dev)) for x, y in host]
+
+    def step(i, e2e):
+        x, y = host[i % 8] if e2e else devb[i % 8]
+        if e2e:
+            x, y = x.to(dev, non_blocking=True), y.to(dev, non_blocking=True)
+        loss = rep.step(inputs=x if rep.stage == 0 else None, labels=y if rep.stage == 1 else None)
+        return loss.item() if (e2e and loss is not None) else loss
+
+    def fence():
+        dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(e2e):
+        fence()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for i in range(args.steps):
+            step(i, e2e)
+        b.record()
+        fence()
+        t = torch.tensor([a.elapsed_time(b) * 1e-3], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    for i in range(max(args.settle, 3) + args.warmup):
+        step(i, False)
+    l0 = rep.optimizer.launches
+    clocks = ClockSampler(local) if rank == 0 else None
+    t_dev = timed(False)
+    launches = rep.optimizer.launches - l0
+    for i in range(3):
+        step(i, True)
+    t_e2e = timed(True)
+    clk = clocks.stop() if clocks else None
+    R = rep.replicas
+    if rank == 0:
+        line = {"metric": METRIC, "value": R * batch * args.steps / t_dev, "unit": UNIT, "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": t_dev / args.steps * 1e3,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": workload_config("task4", batch, R),
+                "arm": {"where": f"{world} x B200: {R} replicas x 2 stages, one process per GPU", "microbatches": 4,
+                        "algo": args.algo, "sync": "per-stage sub-group, fused with plain SGD (momentum 0)"},
+                "e2e": {"value": R * batch * args.steps / t_e2e, "unit": UNIT,
+                        "h2d_bytes_per_step": host[0][0].numel() * 4 + host[0][1].numel() * 8, "d2h_bytes_per_step": 4,
+                        "ms_per_step": t_e2e / args.steps * 1e3},
+                "gpu_launches": launches, "clocks": clk, "roofline": None,
+                "note": "latency-bound: 25 K / 207 K-element buckets (SURVEY.md section 8d small-message caveat); "
+                        "kernel rooflines are quoted on the ResNet configs"}
+        emit(line)
+    fence()
+    rep.close()
+    dist.destroy_process_group()
+    return 0
+
+
 def gpu_arm(args):
     import torch
     import torch.distributed as dist
@@ -878,6 +960,8 @@ def main():
     os.dup2(2, 1)
     if args.impl == "reference":
         return reference_arm(args)
+    if args.model == "task4":
+        return task4_arm(args)
     return gpu_arm(args)
 
 

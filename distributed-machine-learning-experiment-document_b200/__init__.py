@@ -20,8 +20,9 @@ from .hooks import HookState, comm_hook
 from .optim import SGD, AdamOptimizer, BaseOptimizer, GdOptimizer
 from .runtime import Context, Plan, default_context, opt_args, reset_default_context, sampler_sizes, sgd_args
 from .sampler import DistributedSampler, MySampler
+from .task4 import SubNetConv, SubNetFC, TwoStageReplica
 
 __all__ = ["B200DDPError", "Context", "Plan", "GradSync", "GraphedTrainStep", "SGD", "AdamOptimizer", "GdOptimizer", "BaseOptimizer", "DistributedSampler", "MySampler", "HookState",
            "comm_hook", "dist_utils", "dist_init", "get_local_rank", "get_world_size", "init_parameters",
            "allreduce_average_gradients", "average_gradients", "allgather_average_gradients", "enable_fused_step",
-           "configure", "CommTimer", "broadcast_from_rank0", "default_context", "reset_default_context", "sampler_sizes", "sgd_args", "opt_args"]
+           "configure", "CommTimer", "broadcast_from_rank0", "default_context", "reset_default_context", "sampler_sizes", "sgd_args", "opt_args", "TwoStageReplica", "SubNetConv", "SubNetFC"]

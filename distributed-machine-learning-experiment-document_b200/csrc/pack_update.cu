@@ -262,6 +262,7 @@ template <typename BT, bool FB, bool WG>
 cudaError_t run_update_opt(const b200ddp_plan *plan, const Segment &sg, const void *bucket, const PtrArrays &pa,
                            const SgdScalars &hp, const LaunchCfg &lc, cudaStream_t s) {
     if (hp.rule == kRuleAdam) return run_update_cap<BT, FB, WG, kRuleAdam>(plan, sg, bucket, pa, hp, lc, s);
+    if (hp.rule == kRuleGd) return run_update_cap<BT, FB, WG, kRuleGd>(plan, sg, bucket, pa, hp, lc, s);
     return run_update_cap<BT, FB, WG, kRuleSgd>(plan, sg, bucket, pa, hp, lc, s);
 }
 

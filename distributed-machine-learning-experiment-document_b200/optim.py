@@ -34,6 +34,7 @@ class SGD(Optimizer):
         super().__init__(params, defaults)
         self._plans = {}
         self._engine = None          # set by b200ddp.enable_fused_step
+        self._ctx = None             # context of the direct path (None: the process-wide default)
         self._write_grads = True
         self.launches = 0
 
@@ -92,7 +93,7 @@ class SGD(Optimizer):
             self.launches += eng.launches - before
             eng.pending = False
             return loss
-        ctx = default_context()
+        ctx = self._ctx if self._ctx is not None else default_context()
         for group in self.param_groups:
             params = [p for p in group["params"] if p.grad is not None]
             if not params:

@@ -58,10 +58,10 @@ class FakeCtx:
         self.calls.append(("allreduce", off, nelem, algo))
         return off + (self.staging_bytes if algo == _lib.ALGO_ONESHOT else 0)     # one-shot result is out of place
 
-    def unpack(self, plan, bucket, ptrs, divisor):
+    def unpack(self, plan, bucket, ptrs, divisor, stream=None):
         self.calls.append(("unpack", bucket - self.staging_ptr, divisor))
 
-    def unpack_sgd(self, plan, bucket, ps, ms, gs, args):
+    def unpack_sgd(self, plan, bucket, ps, ms, gs, args, stream=None):
         self.calls.append(("unpack_sgd", bucket - self.staging_ptr, args.grad_divisor, args.first_step, gs is not None))
 
     def allreduce_sgd(self, plan, off, ps, ms, gs, args):

@@ -583,3 +583,52 @@ def test_ddp_comm_hook_more_ranks(ws):
 
 def test_next_rows_four_ranks():
     _run(4, _next_rows)
+
+
+def _task4_dp(rank, ws, microbatches):
+    """R replicas x 2 stages (BASELINE.json configs[3]) against plain data parallelism of the WHOLE lab
+    CNN over R ranks, computed locally by every rank from all replicas' batches: same split
+    (codes/task4/model.py:18-46), plain SGD lr=0.01 (:126), gradient = mean over replicas
+    (codes/task4/dist_utils.py:40-46)."""
+    import b200ddp
+    from oracle import ref_ddp
+    R = ws // 2
+    rep = b200ddp.TwoStageReplica(lr=0.01, microbatches=microbatches, seed=4)
+    torch.manual_seed(4)
+    full = ref_ddp.LabNet().cuda()
+    loss_fn = torch.nn.CrossEntropyLoss()
+    for s in range(4):
+        batches = [ref_ddp.synthetic_batch(r, s, 32, (1, 28, 28), 10) for r in range(R)]
+        x, y = batches[rep.replica]
+        loss = rep.step(inputs=x.cuda() if rep.stage == 0 else None, labels=y.cuda() if rep.stage == 1 else None)
+        # expected: mean over replicas of the full model's gradients, then p <- p - lr * g
+        grads = []
+        for bx, by in batches:
+            full.zero_grad(set_to_none=True)
+            loss_fn(full(bx.cuda()), by.cuda()).backward()
+            grads.append([p.grad.clone() for p in full.parameters()])
+        with torch.no_grad():
+            for i, p in enumerate(full.parameters()):
+                acc = grads[0][i].clone()
+                for g in grads[1:]:
+                    acc += g[i]
+                p.add_(acc / R, alpha=-0.01)
+        if rep.stage == 1:
+            assert loss is not None and torch.isfinite(loss)
+    want = list(full.parameters())[:4] if rep.stage == 0 else list(full.parameters())[4:]
+    for p, w in zip(rep.params, want):
+        assert p.shape == w.shape
+        assert (p.detach() - w.detach()).abs().max() <= 1e-5 * w.detach().abs().max(), "stage diverged from full-model data parallelism"
+    # replicas of a stage hold identical bits
+    flat = torch.cat([p.detach().flatten() for p in rep.params])
+    ref0 = flat.clone()
+    torch.distributed.broadcast(ref0, rep.stage, group=rep.group)          # global rank of replica 0 of this stage
+    assert torch.equal(flat, ref0), "replicas diverged"
+    torch.cuda.synchronize()
+    torch.distributed.barrier()
+    rep.close()
+
+
+@pytest.mark.parametrize("ws,microbatches", [(2, 1), (4, 1), (4, 4), (8, 2)])
+def test_task4_two_stage_replicated(ws, microbatches):
+    _run(ws, _task4_dp, microbatches)
