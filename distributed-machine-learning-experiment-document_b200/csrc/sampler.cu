@@ -240,7 +240,11 @@ sampler_cluster_kernel(uint32_t *draws, uint32_t *resv, int32_t *perm, uint32_t 
     }
     unsigned int *pend0 = cluster.map_shared_rank(pend, 0);
 
+    bool overflow = false;
     for (uint32_t round = 1;; ++round) {
+        // the round number shares the reservation word with the priority (16 bits each); the same bound
+        // on every thread, so all CTAs leave together.  Never reached in practice (depth is O(log n)).
+        if (round >= (uint32_t)kMaxRounds) { overflow = true; break; }
 #pragma unroll
         for (int k = 0; k < kClusterIters; ++k)
             if (mask & (1u << k)) {
@@ -290,7 +294,7 @@ sampler_cluster_kernel(uint32_t *draws, uint32_t *resv, int32_t *perm, uint32_t 
 
     for (int64_t k = gtid; k < num_samples; k += nthreads) {
         const uint32_t src = (uint32_t)padded_source((int64_t)rank + (int64_t)world * k, (int64_t)n);
-        out[k] = (int64_t)__ldcg(perm + src);
+        out[k] = overflow ? (int64_t)-1 : (int64_t)__ldcg(perm + src);
     }
     cluster.sync();   // block 0's `pend` may still be read by the others until here
 }

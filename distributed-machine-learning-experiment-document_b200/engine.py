@@ -19,6 +19,8 @@ values are the same, only the time at which the work starts differs.
 """
 from __future__ import annotations
 
+import os
+
 import torch
 
 from . import _lib
@@ -29,8 +31,8 @@ from .runtime import Context, Plan, default_context, dtype_code, opt_args, sgd_a
 # kernel stay a small part of each.  Buckets that run while backward still computes use few blocks,
 # like NCCL's channels: a full-GPU grid of blocks spinning on their peers takes the SMs backward needs
 # (measured: 2 ranks, ResNet-18, full grids -> 2.13 ms / step, slower than no overlap at all).
-DEFAULT_OVERLAP_CAP = 8 << 20
-OVERLAP_BLOCKS = 32
+DEFAULT_OVERLAP_CAP = int(float(os.environ.get("B200DDP_OVERLAP_CAP_MB", "8")) * (1 << 20))
+OVERLAP_BLOCKS = int(os.environ.get("B200DDP_OVERLAP_BLOCKS", "32"))
 
 
 def _is_pow2(n: int) -> bool:
@@ -85,7 +87,7 @@ def split_buckets_reverse(numels, esize: int, cap_bytes, staging_bytes: int):
 
 
 class _Bucket:
-    __slots__ = ("lo", "hi", "plan", "offset", "result_offset", "algo", "ready", "launched", "fused_pending")
+    __slots__ = ("lo", "hi", "plan", "offset", "result_offset", "algo", "ready", "launched", "fused_pending", "done")
 
     def __init__(self, lo, hi, plan, offset):
         self.lo, self.hi, self.plan, self.offset = lo, hi, plan, offset
@@ -94,6 +96,7 @@ class _Bucket:
         self.ready = 0               # gradients of this bucket accumulated since the last sync
         self.launched = False        # pack + reduce already enqueued (overlap mode)
         self.fused_pending = False   # reduction left to the fused one-shot update
+        self.done = None             # overlap: event recorded behind this bucket's reduction
 
 
 class GradSync:
@@ -136,7 +139,9 @@ class GradSync:
         self._p2p_blocks = 0
         if self.overlap:
             self._p2p_blocks = self.ctx.get_option("p2p_blocks")
+            # two side streams: pack + reduce of bucket k+1 must not queue behind the update of bucket k
             self._side = torch.cuda.Stream(device=self.params[0].device)
+            self._upd = torch.cuda.Stream(device=self.params[0].device)
             owner = {}
             for bi, b in enumerate(self.buckets):
                 for p in self.params[b.lo:b.hi]:
@@ -218,6 +223,8 @@ class GradSync:
             finally:
                 if not last:
                     self.ctx.set_option("p2p_blocks", self._p2p_blocks)
+            b.done = torch.cuda.Event()
+            b.done.record(self._side)
             b.launched = True
             self._next += 1
 
@@ -251,15 +258,17 @@ class GradSync:
             return            # all_reduce over one rank and a division by 1 change nothing
         _, divisor = self._scales()
         early = self.overlap and self._finish_overlap()
-        stream = self._side if early else None
+        stream = self._upd if early else None
         for b in self.buckets:
             gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])
             if not early:
                 self._pack_and_reduce(b, gs, fuse_oneshot=False)
+            else:
+                self._upd.wait_event(b.done)
             self.ctx.unpack(b.plan, self.ctx.bucket_ptr(b.result_offset), gs, divisor, stream)
             self.launches += 1
         if early:
-            torch.cuda.current_stream().wait_stream(self._side)
+            torch.cuda.current_stream().wait_stream(self._upd)
         if self.overlap:
             self._reset_overlap()
 
@@ -277,12 +286,14 @@ class GradSync:
             args = opt_args(rule, grad_divisor=divisor, **hyper)
             has_mom = rule == "adam"
         early = self.overlap and self._finish_overlap()
-        stream = self._side if early else None
+        stream = self._upd if early else None
         for b in self.buckets:
             gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])      # gathered once, used by pack and update
             fused = False
             if not early:
                 fused = self._pack_and_reduce(b, gs, fuse_oneshot=(rule == "sgd"))
+            else:
+                self._upd.wait_event(b.done)
             ps = [p.data_ptr() for p in self.params[b.lo:b.hi]]
             ms = [m.data_ptr() for m in moms[b.lo:b.hi]] if has_mom else None
             go = gs if write_grads else None
@@ -295,7 +306,7 @@ class GradSync:
                 self.ctx.unpack_sgd(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, go, args, stream)
             self.launches += 1
         if early:
-            torch.cuda.current_stream().wait_stream(self._side)
+            torch.cuda.current_stream().wait_stream(self._upd)
         if self.overlap:
             self._reset_overlap()
 

@@ -342,6 +342,9 @@ def sampler_shard_static(out: torch.Tensor, n, world, rank, seed=0, epoch=0, shu
     fits = n <= _lib.SAMPLER_STATIC_MAX_N     # beyond the limit the library's own refusal is the error to show
     if fits and (out.dtype != torch.int64 or not out.is_cuda or not out.is_contiguous() or out.numel() < max(num, 0)):
         raise B200DDPError(f"out must be a contiguous int64 CUDA tensor with at least {num} elements")
+    if fits and out.is_cuda and out.device.index != torch.cuda.current_device():
+        raise B200DDPError(f"out lives on cuda:{out.device.index} but the current device is "
+                           f"cuda:{torch.cuda.current_device()}: the entry point works on the current device")
     check(_lib.lib().b200ddp_sampler_shard_static(int(n), int(world), int(rank), int(seed) & 0xFFFFFFFFFFFFFFFF,
                                                   int(epoch) & 0xFFFFFFFFFFFFFFFF, int(bool(shuffle)),
                                                   int(bool(drop_last)),

@@ -45,6 +45,8 @@ class DistributedSampler(Sampler):
 
     def __iter__(self):
         indices = self.device_indices().cpu().tolist()
+        if indices and indices[0] < 0:
+            raise RuntimeError("the device shuffle did not finish within its round budget (see include/b200ddp.h)")
         if len(indices) != self.num_samples:
             raise AssertionError(f"Number of subsampled indices ({len(indices)}) does not match "
                                  f"num_samples ({self.num_samples})")

@@ -228,7 +228,12 @@ int b200ddp_emu_allreduce_sgd(b200ddp_ctx *const *ctxs, b200ddp_plan *const *pla
  * out_dev receives num_samples int64 indices, bit-exact with torch.
  * n must be below 2^32/20 (torch switches to 64-bit draws there).
  * Uses scratch owned by ctx (grown with cudaMalloc on first use of a larger n,
- * which synchronises). */
+ * which synchronises).  The scratch is shared by all calls on this ctx: keep them on one stream (or
+ * order the streams) - calls that overlap on the GPU race on it.
+ * The call is asynchronous, so a failure inside the kernel cannot come back as a return code: if the
+ * shuffle does not finish within its round budget (4096 rounds; the expected depth is ~2.5 log2 n, 37
+ * at n = 60,000 - never observed) every element of out_dev is set to -1.  The Python sampler checks
+ * for that when it copies the shard to the host. */
 int b200ddp_sampler_sizes(int64_t n, int world, int drop_last, int64_t *num_samples,
                           int64_t *total_size);
 int b200ddp_sampler_shard(b200ddp_ctx *ctx, int64_t n, int world, int rank, uint64_t seed,
