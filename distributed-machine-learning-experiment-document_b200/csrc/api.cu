@@ -108,6 +108,10 @@ static int set_option(b200ddp_ctx *ctx, int option, long long v) {
             B2_REQUIRE(v == 2 || v == 4 || v == 8, B200DDP_EINVAL, "copy unroll must be 2, 4 or 8");
             ctx->copy_unroll = (int)v;
             return B200DDP_OK;
+        case B200DDP_OPT_HBM_BLOCKS_PER_SM:
+            B2_REQUIRE(v >= 0 && v <= 32, B200DDP_EINVAL, "blocks per SM %lld not in [0, 32]", v);
+            ctx->hbm_blocks_per_sm = (int)v;
+            return B200DDP_OK;
         case B200DDP_OPT_TRACE: {
             if (v != 0 && ctx->trace == nullptr) {
                 B2_CHECK_CUDA(cudaSetDevice(ctx->device));
@@ -286,6 +290,7 @@ int b200ddp_get_option(const b200ddp_ctx *ctx, int option, long long *value) {
         case B200DDP_OPT_NVLS_DEPTH: *value = ctx->nvls_depth; break;
         case B200DDP_OPT_COPY_UNROLL: *value = ctx->copy_unroll; break;
         case B200DDP_OPT_TRACE: *value = ctx->trace != nullptr; break;
+        case B200DDP_OPT_HBM_BLOCKS_PER_SM: *value = ctx->hbm_blocks_per_sm; break;
         default: set_error("unknown option %d", option); return B200DDP_EINVAL;
     }
     return B200DDP_OK;

@@ -125,6 +125,7 @@ struct LaunchCfg {    // per-context launch settings, read at every call
     int sm_count;
     bool pdl;         // launch with the programmatic-stream-serialization attribute
     int div_mode;     // B200DDP_DIV_*
+    int blocks_per_sm;   // grid cap of pack / unpack / update in blocks per SM; 0: as many as fit (occupancy)
 };
 
 struct PeerTable {    // kernel parameter of the P2P kernels
@@ -157,7 +158,8 @@ struct b200ddp_ctx {
     int p2p_blocks = 0;                // 0: built-in grid cap
     int nvls_depth = 0;                // 0: built-in number of multimem loads in flight per thread
     unsigned long long *trace = nullptr;   // B200DDP_OPT_TRACE: 4 time stamps per block of the last P2P launch
-    b200ddp::LaunchCfg lc() const { return b200ddp::LaunchCfg{sm_count, pdl, div_mode}; }
+    int hbm_blocks_per_sm = 0;         // 0: pack / unpack / update fill the GPU; n: at most n blocks per SM
+    b200ddp::LaunchCfg lc() const { return b200ddp::LaunchCfg{sm_count, pdl, div_mode, hbm_blocks_per_sm}; }
     // sampler scratch
     void *sampler_scratch = nullptr;
     size_t sampler_scratch_bytes = 0;

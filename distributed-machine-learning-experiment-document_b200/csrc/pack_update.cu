@@ -180,13 +180,14 @@ __global__ void __launch_bounds__(kThreads) update_kernel(const __grid_constant_
 }
 
 // Occupancy is a property of the kernel, not of the launch: query once per instantiation.
-template <typename K> int grid_for(K kernel, int &blocks_per_sm, int nchunks, int sm_count) {
+template <typename K> int grid_for(K kernel, int &blocks_per_sm, int nchunks, const LaunchCfg &lc) {
     if (blocks_per_sm == 0) {
         int n = 0;
         if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, kThreads, 0) != cudaSuccess || n < 1) n = 1;
         blocks_per_sm = n;
     }
-    const int g = sm_count * blocks_per_sm;
+    const int per = lc.blocks_per_sm > 0 && lc.blocks_per_sm < blocks_per_sm ? lc.blocks_per_sm : blocks_per_sm;
+    const int g = lc.sm_count * per;
     return nchunks < g ? nchunks : g;
 }
 
@@ -209,7 +210,7 @@ cudaError_t run_pack(const b200ddp_plan *plan, const Segment &sg, const void *co
     const void *const *kinds[1] = {grads};
     fill_tab(tab, plan, sg, kinds);
     const int n = sg.k1 - sg.k0;
-    return launch_ex(pack_kernel<BT, CAP, U>, grid_for(pack_kernel<BT, CAP, U>, occ, n, lc.sm_count), kThreads, s, lc.pdl,
+    return launch_ex(pack_kernel<BT, CAP, U>, grid_for(pack_kernel<BT, CAP, U>, occ, n, lc), kThreads, s, lc.pdl,
                      tab, (const Chunk *)(plan->d_copy_chunks + sg.k0), n, (BT *)bucket, scale);
 }
 template <typename BT, int CAP, int U>
@@ -221,7 +222,7 @@ cudaError_t run_unpack(const b200ddp_plan *plan, const Segment &sg, const void *
     fill_tab(tab, plan, sg, kinds);
     const int n = sg.k1 - sg.k0;
     const Divisor dv = make_divisor(divisor, lc.div_mode);
-    return launch_ex(unpack_kernel<BT, CAP, U>, grid_for(unpack_kernel<BT, CAP, U>, occ, n, lc.sm_count), kThreads, s,
+    return launch_ex(unpack_kernel<BT, CAP, U>, grid_for(unpack_kernel<BT, CAP, U>, occ, n, lc), kThreads, s,
                      lc.pdl, tab, (const Chunk *)(plan->d_copy_chunks + sg.k0), n, (const BT *)bucket, dv);
 }
 template <typename BT, int CAP>
@@ -249,7 +250,7 @@ cudaError_t run_update(const b200ddp_plan *plan, const Segment &sg, const void *
     TensorTab<CAP, kNumPtrKinds> tab;
     fill_tab(tab, plan, sg, pa.k);
     const int n = sg.c1 - sg.c0;
-    return launch_ex(update_kernel<BT, FB, WG, OPT, CAP>, grid_for(update_kernel<BT, FB, WG, OPT, CAP>, occ, n, lc.sm_count),
+    return launch_ex(update_kernel<BT, FB, WG, OPT, CAP>, grid_for(update_kernel<BT, FB, WG, OPT, CAP>, occ, n, lc),
                      kThreads, s, lc.pdl, tab, (const Chunk *)(plan->d_chunks + sg.c0), n, (const BT *)bucket, hp);
 }
 template <typename BT, bool FB, bool WG, int OPT>

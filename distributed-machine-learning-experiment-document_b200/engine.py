@@ -33,6 +33,9 @@ from .runtime import Context, Plan, default_context, dtype_code, opt_args, sgd_a
 # (measured: 2 ranks, ResNet-18, full grids -> 2.13 ms / step, slower than no overlap at all).
 DEFAULT_OVERLAP_CAP = int(float(os.environ.get("B200DDP_OVERLAP_CAP_MB", "8")) * (1 << 20))
 OVERLAP_BLOCKS = int(os.environ.get("B200DDP_OVERLAP_BLOCKS", "32"))
+# ... and the HBM-bound kernels of those buckets (pack, update) take at most this many blocks per SM, so that
+# backward's kernels find free slots beside them (0: fill the GPU)
+OVERLAP_HBM_BLOCKS_PER_SM = int(os.environ.get("B200DDP_OVERLAP_HBM_BLOCKS", "2"))
 
 
 def _is_pow2(n: int) -> bool:
@@ -215,18 +218,35 @@ class GradSync:
                 self._side.wait_stream(main)
                 forked = True
             gs = _lib.ptr_array([g.data_ptr() for g in self._grads(b)])
-            last = self._next == len(self.buckets) - 1        # nothing left to hide behind: full grid
-            if not last:
-                self.ctx.set_option("p2p_blocks", OVERLAP_BLOCKS)
-            try:
+            last = self._next == len(self.buckets) - 1        # nothing left to hide behind: full grids
+            with self._hidden(not last):
                 b.fused_pending = self._pack_and_reduce(b, gs, fuse_oneshot=False, stream=self._side)
-            finally:
-                if not last:
-                    self.ctx.set_option("p2p_blocks", self._p2p_blocks)
             b.done = torch.cuda.Event()
             b.done.record(self._side)
             b.launched = True
             self._next += 1
+
+    def _hidden(self, on: bool):
+        """Launch settings for kernels that run beside backward (see OVERLAP_* above): small grids, and
+        NO programmatic dependent launch - behind a reduction that is still waiting for its peers, a
+        pre-launched pack parks its blocks in griddepcontrol.wait and backward's kernels find no free
+        SM slot until the reduction ends.  The last bucket (on=False) has nothing beside it and keeps
+        the context's settings."""
+        eng = self
+
+        class _Ctx:
+            def __enter__(self):
+                eng._saved = {}
+                if on:
+                    eng._saved = {k: eng.ctx.get_option(k) for k in ("p2p_blocks", "hbm_blocks_per_sm", "pdl")}
+                    eng.ctx.set_option("pdl", int(os.environ.get("B200DDP_OVERLAP_PDL", "0")))
+                    eng.ctx.set_option("p2p_blocks", OVERLAP_BLOCKS).set_option("hbm_blocks_per_sm", OVERLAP_HBM_BLOCKS_PER_SM)
+
+            def __exit__(self, *exc):
+                for k, v in eng._saved.items():
+                    eng.ctx.set_option(k, v)
+                return False
+        return _Ctx()
 
     def _finish_overlap(self):
         """After backward: whatever has not left yet leaves now (on the side stream).  Returns False
@@ -297,18 +317,25 @@ class GradSync:
             ps = [p.data_ptr() for p in self.params[b.lo:b.hi]]
             ms = [m.data_ptr() for m in moms[b.lo:b.hi]] if has_mom else None
             go = gs if write_grads else None
-            if rule != "sgd":
-                vs = [v.data_ptr() for v in vels[b.lo:b.hi]] if rule == "adam" else None
-                self.ctx.unpack_opt(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, vs, go, args, stream)
+            if early:
+                with self._hidden(b is not self.buckets[-1]):
+                    self._update(b, rule, ps, ms, vels, go, args, stream)
             elif fused:
                 self.ctx.allreduce_sgd(b.plan, b.offset, ps, ms, go, args)
             else:
-                self.ctx.unpack_sgd(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, go, args, stream)
+                self._update(b, rule, ps, ms, vels, go, args, stream)
             self.launches += 1
         if early:
             torch.cuda.current_stream().wait_stream(self._upd)
         if self.overlap:
             self._reset_overlap()
+
+    def _update(self, b, rule, ps, ms, vels, go, args, stream):
+        if rule != "sgd":
+            vs = [v.data_ptr() for v in vels[b.lo:b.hi]] if rule == "adam" else None
+            self.ctx.unpack_opt(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, vs, go, args, stream)
+        else:
+            self.ctx.unpack_sgd(b.plan, self.ctx.bucket_ptr(b.result_offset), ps, ms, go, args, stream)
 
     def close(self):
         for h in self._hooks:

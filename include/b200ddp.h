@@ -48,7 +48,9 @@ enum { B200DDP_OPT_DIV_MODE = 1,          /* B200DDP_DIV_*                      
        B200DDP_OPT_P2P_BLOCKS = 6,        /* grid cap of the P2P / NVLS kernels; 0: built-in (2 per SM)       */
        B200DDP_OPT_NVLS_DEPTH = 7,        /* multimem loads in flight per thread (1, 2, 4, 8); 0: built-in    */
        B200DDP_OPT_COPY_UNROLL = 8,       /* 128-bit accesses per thread in pack / unpack (2, 4, 8); new plans */
-       B200DDP_OPT_TRACE = 9 };           /* 1: the cross-GPU kernels stamp their phases (b200ddp_trace_read)   */
+       B200DDP_OPT_TRACE = 9,             /* 1: the cross-GPU kernels stamp their phases (b200ddp_trace_read)   */
+       B200DDP_OPT_HBM_BLOCKS_PER_SM = 10 }; /* grid cap of pack / unpack / update, blocks per SM; 0: fill the GPU.
+                                              A small value leaves SM slots to kernels of other streams.          */
 
 #define B200DDP_MAX_WORLD 8
 #define B200DDP_IPC_BYTES 128   /* staging handle (64 B) + flag handle (64 B) */
