@@ -54,8 +54,10 @@ def parse():
                     help="fused: sync folded into optimizer.step(); strict: p.grad averaged first")
     ap.add_argument("--step", default="graph", choices=["graph", "eager"],
                     help="graph: the loop body replayed from a CUDA graph; eager: the reference's Python loop")
-    ap.add_argument("--overlap", default="auto", choices=["auto", "on", "off"],
-                    help="start each bucket's pack + all-reduce from inside backward (auto: on when N > 1)")
+    ap.add_argument("--overlap", default="off", choices=["on", "off"],
+                    help="start each bucket's pack + all-reduce from inside backward on side streams.  Off by default: "
+                         "measured on 2 x B200 (profiles/r02_overlap_n2.md) a second branch in the replayed CUDA graph "
+                         "slows the ~320 small kernels of this step's main branch by more than the overlap hides")
     ap.add_argument("--no-parity-check", action="store_true", help="skip the N > 1 self-check against NCCL / exact sums")
     ap.add_argument("--no-torch-baseline", action="store_true",
                     help="skip timing the reference's own GPU path (per-parameter NCCL all_reduce + torch.optim.SGD)")
@@ -732,7 +734,7 @@ def gpu_arm(args):
     name, batch, lr = MODELS[args.model]
     batch = args.batch or batch
     bucket_dtype = args.bucket_dtype or ("bf16" if args.model == "resnet50" else "fp32")
-    overlap = world > 1 and args.overlap != "off"
+    overlap = world > 1 and args.overlap == "on"
     b200ddp.configure(bucket_dtype=bucket_dtype, algo=args.algo, overlap=overlap)
 
     model, chw, classes = build_model(name)
