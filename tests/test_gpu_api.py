@@ -179,3 +179,42 @@ def test_graphed_train_step_equals_eager_loop(default_ctx, fused):
     assert l0 == l1
     for a, b in zip(p0 + m0 + g0, p1 + m1 + g1):
         assert torch.equal(a, b)
+
+
+def test_context_options_round_trip_and_reject_bad_values(ctx1):
+    """b200ddp_set_option / b200ddp_get_option (include/b200ddp.h, B200DDP_OPT_*)."""
+    assert ctx1.get_option("div_mode") == b200ddp._lib.DIV_RECIPROCAL       # the documented default
+    assert ctx1.get_option("peer_timeout_ms") == 0                          # wait for ever, like NCCL
+    for name, value in (("div_mode", "ieee"), ("pdl", 0), ("nvls_min_bytes", 1 << 20), ("oneshot_max_bytes", 4096),
+                        ("peer_timeout_ms", 1500), ("p2p_blocks", 64), ("nvls_depth", 8), ("copy_unroll", 8),
+                        ("hbm_blocks_per_sm", 2), ("trace", 1)):
+        ctx1.set_option(name, value)
+        want = {"ieee": b200ddp._lib.DIV_IEEE}.get(value, value)
+        assert ctx1.get_option(name) == want, name
+    for name, value in (("div_mode", 7), ("p2p_blocks", 100000), ("nvls_depth", 3), ("copy_unroll", 5),
+                        ("hbm_blocks_per_sm", -1)):
+        with pytest.raises(b200ddp.B200DDPError):
+            ctx1.set_option(name, value)
+    ctx1.set_option("trace", 0)
+    with pytest.raises(b200ddp.B200DDPError, match="tracing is off"):
+        ctx1.trace_read(4)
+
+
+@pytest.mark.parametrize("unroll", [2, 4, 8])
+@pytest.mark.parametrize("blocks_per_sm", [0, 1])
+def test_pack_unpack_launch_settings_do_not_change_results(ctx1, unroll, blocks_per_sm):
+    """copy_unroll changes the chunking of pack / unpack, hbm_blocks_per_sm their grid: same bytes out."""
+    ctx1.set_option("copy_unroll", unroll).set_option("hbm_blocks_per_sm", blocks_per_sm)
+    numels = list(synth.RAGGED_NUMELS) + [100_003, 8192 * 3]
+    plan = ctx1.plan(numels)
+    src = [torch.from_numpy(synth.dense_grad(n, 0, 0, t)).cuda() for t, n in enumerate(numels)]
+    out = [torch.full_like(t, float("nan")) for t in src]
+    ctx1.pack_scale(plan, [t.data_ptr() for t in src], ctx1.bucket_ptr(0), 0.25)
+    ctx1.unpack(plan, ctx1.bucket_ptr(0), [t.data_ptr() for t in out], 1.0)
+    for a, b in zip(src, out):
+        assert torch.equal(a * 0.25, b)
+    # and the update kernel under the grid cap
+    p = [torch.ones_like(t) for t in src]
+    ctx1.unpack_sgd(plan, ctx1.bucket_ptr(0), [t.data_ptr() for t in p], None, None, b200ddp.sgd_args(lr=1.0))
+    for a, b in zip(src, p):
+        assert torch.equal(b, 1.0 - a * 0.25)
