@@ -13,11 +13,12 @@ from ctypes import (POINTER, Structure, byref, c_char_p, c_double, c_float, c_in
 F32, BF16 = 0, 1
 DIV_IEEE, DIV_RECIPROCAL = 0, 1
 (OPT_DIV_MODE, OPT_PDL, OPT_NVLS_MIN_BYTES, OPT_ONESHOT_MAX_BYTES, OPT_PEER_TIMEOUT_MS, OPT_P2P_BLOCKS,
- OPT_NVLS_DEPTH, OPT_COPY_UNROLL, OPT_TRACE, OPT_HBM_BLOCKS_PER_SM) = range(1, 11)
+ OPT_NVLS_DEPTH, OPT_COPY_UNROLL, OPT_TRACE, OPT_HBM_BLOCKS_PER_SM, OPT_NVLS_BLOCKS) = range(1, 12)
 OPTIONS = {"div_mode": OPT_DIV_MODE, "pdl": OPT_PDL, "nvls_min_bytes": OPT_NVLS_MIN_BYTES,
            "oneshot_max_bytes": OPT_ONESHOT_MAX_BYTES, "peer_timeout_ms": OPT_PEER_TIMEOUT_MS,
            "p2p_blocks": OPT_P2P_BLOCKS, "nvls_depth": OPT_NVLS_DEPTH, "copy_unroll": OPT_COPY_UNROLL,
-           "trace": OPT_TRACE, "hbm_blocks_per_sm": OPT_HBM_BLOCKS_PER_SM}
+           "trace": OPT_TRACE, "hbm_blocks_per_sm": OPT_HBM_BLOCKS_PER_SM,
+           "nvls_blocks": OPT_NVLS_BLOCKS}
 RULE_ADAM, RULE_GD = 1, 2
 MAX_BLOCKS_P2P = 1024
 ALGO_AUTO, ALGO_NCCL, ALGO_ONESHOT, ALGO_TWOSHOT, ALGO_NVLS = 0, 1, 2, 3, 4

@@ -108,6 +108,10 @@ static int set_option(b200ddp_ctx *ctx, int option, long long v) {
             B2_REQUIRE(v == 2 || v == 4 || v == 8, B200DDP_EINVAL, "copy unroll must be 2, 4 or 8");
             ctx->copy_unroll = (int)v;
             return B200DDP_OK;
+        case B200DDP_OPT_NVLS_BLOCKS:
+            B2_REQUIRE(v >= 0 && v <= kMaxBlocksP2P, B200DDP_EINVAL, "block cap %lld not in [0, %d]", v, kMaxBlocksP2P);
+            ctx->nvls_blocks = (int)v;
+            return B200DDP_OK;
         case B200DDP_OPT_HBM_BLOCKS_PER_SM:
             B2_REQUIRE(v >= 0 && v <= 32, B200DDP_EINVAL, "blocks per SM %lld not in [0, 32]", v);
             ctx->hbm_blocks_per_sm = (int)v;
@@ -191,6 +195,7 @@ int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200dd
     set_option(ctx, B200DDP_OPT_PEER_TIMEOUT_MS, env_ll("B200DDP_PEER_TIMEOUT_MS", 0));
     set_option(ctx, B200DDP_OPT_P2P_BLOCKS, env_ll("B200DDP_P2P_BLOCKS", 0));
     set_option(ctx, B200DDP_OPT_NVLS_DEPTH, env_ll("B200DDP_NVLS_DEPTH", 0));
+    set_option(ctx, B200DDP_OPT_NVLS_BLOCKS, env_ll("B200DDP_NVLS_BLOCKS", 0));
     const size_t flag_bytes = sizeof(uint32_t) * kMaxBlocksP2P * B200DDP_MAX_WORLD;
     cudaError_t e = cudaMalloc((void **)&ctx->staging, 2 * ctx->staging_bytes + 256);
     if (e == cudaSuccess) e = cudaMalloc((void **)&ctx->flags, flag_bytes);
@@ -291,6 +296,7 @@ int b200ddp_get_option(const b200ddp_ctx *ctx, int option, long long *value) {
         case B200DDP_OPT_COPY_UNROLL: *value = ctx->copy_unroll; break;
         case B200DDP_OPT_TRACE: *value = ctx->trace != nullptr; break;
         case B200DDP_OPT_HBM_BLOCKS_PER_SM: *value = ctx->hbm_blocks_per_sm; break;
+        case B200DDP_OPT_NVLS_BLOCKS: *value = ctx->nvls_blocks; break;
         default: set_error("unknown option %d", option); return B200DDP_EINVAL;
     }
     return B200DDP_OK;

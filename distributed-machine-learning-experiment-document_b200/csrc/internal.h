@@ -157,6 +157,7 @@ struct b200ddp_ctx {
     long long peer_timeout_ms = 0;     // 0: wait for ever, as an NCCL collective does
     int p2p_blocks = 0;                // 0: built-in grid cap
     int nvls_depth = 0;                // 0: built-in number of multimem loads in flight per thread
+    int nvls_blocks = 0;               // 0: built-in grid cap of the in-switch kernel
     unsigned long long *trace = nullptr;   // B200DDP_OPT_TRACE: 4 time stamps per block of the last P2P launch
     int hbm_blocks_per_sm = 0;         // 0: pack / unpack / update fill the GPU; n: at most n blocks per SM
     b200ddp::LaunchCfg lc() const { return b200ddp::LaunchCfg{sm_count, pdl, div_mode, hbm_blocks_per_sm}; }

@@ -24,7 +24,8 @@ namespace b200ddp {
 namespace {
 
 constexpr int kP2PThreads = 512;
-constexpr int kNvlsDepthDefault = 4;   // multimem loads in flight per thread (profiles/r02_sweep_n8_nvls_variants.jsonl)
+constexpr int kNvlsDepthDefault = 1;   // multimem loads in flight per thread  } profiles/r02_sweep_n{2,4,8}_fp32_variants.jsonl:
+constexpr int kNvlsBlocksDefault = 74;   // grid cap of the in-switch kernel      } fewer and shallower is faster
 
 __device__ __forceinline__ void st_release_sys(uint32_t *p, uint32_t v) {
     asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
@@ -538,7 +539,10 @@ int launch_barrier(b200ddp_ctx *ctx, cudaStream_t s) {
 
 int launch_nvls_allreduce(b200ddp_ctx *ctx, size_t off, int64_t nelem, int dtype, cudaStream_t s) {
     P2PArgs a = make_args(ctx, off, nelem, dtype);
-    const int want = p2p_grid_for(nelem, dtype, B200DDP_ALGO_NVLS, ctx->world, block_cap(ctx));
+    // The in-switch kernel wants FEWER blocks than the peer-load kernels: measured on 2, 4 and 8 GPUs
+    // (profiles/r02_sweep_n*_fp32_variants.jsonl) a grid of 74-148 blocks beats 296 at every size from 4 MB up.
+    int cap = ctx->nvls_blocks > 0 ? ctx->nvls_blocks : (ctx->p2p_blocks > 0 ? ctx->p2p_blocks : kNvlsBlocksDefault);
+    const int want = p2p_grid_for(nelem, dtype, B200DDP_ALGO_NVLS, ctx->world, cap);
     cudaError_t e;
 #define B2_NVLS_T(BT, D) \
     launch_ex(nvls_kernel<BT, D>, resident_clamp(ctx, nvls_kernel<BT, D>, kP2PThreads, want), kP2PThreads, s, ctx->pdl, a, ctx->mc_ptr)

@@ -49,6 +49,7 @@ enum { B200DDP_OPT_DIV_MODE = 1,          /* B200DDP_DIV_*                      
        B200DDP_OPT_NVLS_DEPTH = 7,        /* multimem loads in flight per thread (1, 2, 4, 8); 0: built-in    */
        B200DDP_OPT_COPY_UNROLL = 8,       /* 128-bit accesses per thread in pack / unpack (2, 4, 8); new plans */
        B200DDP_OPT_TRACE = 9,             /* 1: the cross-GPU kernels stamp their phases (b200ddp_trace_read)   */
+       B200DDP_OPT_NVLS_BLOCKS = 11,      /* grid cap of the in-switch kernel; 0: built-in                        */
        B200DDP_OPT_HBM_BLOCKS_PER_SM = 10 }; /* grid cap of pack / unpack / update, blocks per SM; 0: fill the GPU.
                                               A small value leaves SM slots to kernels of other streams.          */
 
@@ -71,7 +72,7 @@ int b200ddp_create(int rank, int world, int device, size_t staging_bytes, b200dd
 int b200ddp_destroy(b200ddp_ctx *ctx);
 /* Per-context settings (B200DDP_OPT_*); each has an environment default read at b200ddp_create
  * (B200DDP_DIV_MODE=ieee|reciprocal, B200DDP_PDL, B200DDP_NVLS_MIN_BYTES, B200DDP_ONESHOT_MAX_BYTES,
- * B200DDP_PEER_TIMEOUT_MS, B200DDP_P2P_BLOCKS, B200DDP_NVLS_DEPTH, B200DDP_COPY_UNROLL).  Settings that
+ * B200DDP_PEER_TIMEOUT_MS, B200DDP_P2P_BLOCKS, B200DDP_NVLS_DEPTH, B200DDP_NVLS_BLOCKS, B200DDP_COPY_UNROLL).  Settings that
  * change the shape of a collective launch (grid, algorithm thresholds) must be equal on all ranks. */
 int b200ddp_set_option(b200ddp_ctx *ctx, int option, long long value);
 int b200ddp_get_option(const b200ddp_ctx *ctx, int option, long long *value);

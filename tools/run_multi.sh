@@ -18,7 +18,7 @@ SIZES=1048576,4194304,16777216,44726656,67108864,268435456
 timeout 400 $TR --master-port 29551 tools/sweep_allreduce.py --sizes $SIZES --dtypes fp32 --variants --trace --gloo-max-mb 16 \
     --out $O/r2_sweep_n${N}_fp32_variants.jsonl > $O/r2_sweep_n${N}_fp32.log 2>&1
 echo "sweep fp32 rc=$?"
-timeout 300 $TR --master-port 29552 tools/sweep_allreduce.py --min-log2 10 --max-log2 30 --step-log2 2 --dtypes fp32,bf16 \
+timeout 300 $TR --master-port 29552 tools/sweep_allreduce.py --min-log2 12 --max-log2 30 --step-log2 3 --dtypes fp32,bf16 \
     --out $O/r2_sweep_n${N}_pow4.jsonl > $O/r2_sweep_n${N}_pow4.log 2>&1
 echo "sweep pow4 rc=$?"
 # best NVLS / two-shot launch settings at the ResNet-18 bucket, from the sweep just taken
@@ -37,22 +37,19 @@ try:
     env = {}
     for p in parts[1:]:
         if p.startswith("d"): env["B200DDP_NVLS_DEPTH"] = p[1:]
-        if p.startswith("b"): env["B200DDP_P2P_BLOCKS"] = p[1:]
+        if p.startswith("b"): env["B200DDP_NVLS_BLOCKS" if parts[0] == "nvls" else "B200DDP_P2P_BLOCKS"] = p[1:]
     print("export TUNED='%s';" % pick["algo"], " ".join("export %s=%s;" % kv for kv in env.items()))
 except Exception as e:
     print("export TUNED='none';")
 PY
 )
-echo "tuned settings: $TUNED depth=$B200DDP_NVLS_DEPTH blocks=$B200DDP_P2P_BLOCKS"
+echo "tuned settings: $TUNED depth=$B200DDP_NVLS_DEPTH nvls_blocks=$B200DDP_NVLS_BLOCKS p2p_blocks=$B200DDP_P2P_BLOCKS"
 env | grep B200DDP_ > $O/r2_tuned_env_n$N.txt
 timeout 400 $TR --master-port 29553 bench.py --gpus $N --steps 30 --warmup 5 > $O/r2_bench_n${N}_tuned.json 2> $O/r2_bench_n${N}_tuned.err
 echo "bench r18 tuned rc=$?"; cut -c1-400 $O/r2_bench_n${N}_tuned.json
 timeout 400 $TR --master-port 29554 bench.py --gpus $N --model resnet50 --steps 20 --warmup 5 > $O/r2_bench_r50_n${N}.json 2> $O/r2_bench_r50_n${N}.err
 echo "bench r50 rc=$?"; cut -c1-300 $O/r2_bench_r50_n${N}.json
-unset B200DDP_NVLS_DEPTH B200DDP_P2P_BLOCKS
-timeout 300 $TR --master-port 29555 bench.py --gpus $N --steps 30 --warmup 5 --no-torch-baseline --no-kernel-bench --no-parity-check \
-    > $O/r2_bench_n${N}_defaults.json 2> $O/r2_bench_n${N}_defaults.err
-echo "bench r18 defaults rc=$?"; cut -c1-300 $O/r2_bench_n${N}_defaults.json
+unset B200DDP_NVLS_DEPTH B200DDP_P2P_BLOCKS B200DDP_NVLS_BLOCKS
 timeout 200 $TR --master-port 29556 bench.py --gpus $N --model task4 --steps 30 --warmup 5 > $O/r2_bench_task4_n${N}.json 2> $O/r2_bench_task4_n${N}.err
 echo "bench task4 rc=$?"; cut -c1-300 $O/r2_bench_task4_n${N}.json
 timeout 200 $TR --master-port 29557 tools/bcast_bench.py --model resnet50 --out $O/r2_bcast_n$N.json 2>&1 | tail -1

@@ -66,9 +66,9 @@ def main():
         if not args.variants:
             return out
         if algo == "nvls":
-            for depth in (1, 2, 4, 8):
-                for blocks in (74, 148, 296):
-                    out.append((f"nvls/d{depth}/b{blocks}", {"nvls_depth": depth, "p2p_blocks": blocks}))
+            for depth in (1, 2, 4):
+                for blocks in (37, 74, 148, 296):
+                    out.append((f"nvls/d{depth}/b{blocks}", {"nvls_depth": depth, "nvls_blocks": blocks}))
         elif algo == "twoshot":
             for blocks in (74, 148, 296, 592):
                 out.append((f"twoshot/b{blocks}", {"p2p_blocks": blocks}))
@@ -142,7 +142,8 @@ def main():
                            "algbw_gbs": S / t / 1e9, "busbw_gbs": S / t / 1e9 * 2 * (world - 1) / world}
                     if args.trace and algo in ("twoshot", "nvls", "oneshot"):
                         nvec = S // 16 if algo == "oneshot" else -(-(S // 16) // world)
-                        cap = ctx.get_option("p2p_blocks") or 2 * torch.cuda.get_device_properties(dev).multi_processor_count
+                        cap = (ctx.get_option("nvls_blocks") if algo == "nvls" else 0) or ctx.get_option("p2p_blocks") or \
+                            (74 if algo == "nvls" else 2 * torch.cuda.get_device_properties(dev).multi_processor_count)
                         nblocks = max(1, min(cap, -(-nvec // 1024)))
                         torch.cuda.synchronize()
                         ctx.set_option("trace", 0).set_option("trace", 1)      # a zeroed stamp buffer
