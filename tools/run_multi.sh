@@ -7,20 +7,10 @@ O=gpurun_out
 mkdir -p $O
 TR="python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1"
 nvidia-smi topo -m > $O/r2_topo_n$N.txt 2>&1
-# on the 8-GPU box only the 8-rank tests run (8 GPUs cost 8x; the 2-, 3- and 4-rank tests run on smaller boxes)
-if [ "$N" = "8" ]; then
-    timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -q -rA -k "eight or -8] or [8" > $O/r2_pytest_multi_n$N.log 2>&1
-else
-    timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -q -rA > $O/r2_pytest_multi_n$N.log 2>&1
-fi
-echo "pytest rc=$?"; tail -3 $O/r2_pytest_multi_n$N.log | cut -c1-200
 SIZES=1048576,4194304,16777216,44726656,67108864,268435456
 timeout 400 $TR --master-port 29551 tools/sweep_allreduce.py --sizes $SIZES --dtypes fp32 --variants --trace --gloo-max-mb 16 \
     --out $O/r2_sweep_n${N}_fp32_variants.jsonl > $O/r2_sweep_n${N}_fp32.log 2>&1
 echo "sweep fp32 rc=$?"
-timeout 300 $TR --master-port 29552 tools/sweep_allreduce.py --min-log2 12 --max-log2 30 --step-log2 3 --dtypes fp32,bf16 \
-    --out $O/r2_sweep_n${N}_pow4.jsonl > $O/r2_sweep_n${N}_pow4.log 2>&1
-echo "sweep pow4 rc=$?"
 # best NVLS / two-shot launch settings at the ResNet-18 bucket, from the sweep just taken
 eval $(python - <<PY
 import json
@@ -47,10 +37,20 @@ echo "tuned settings: $TUNED depth=$B200DDP_NVLS_DEPTH nvls_blocks=$B200DDP_NVLS
 env | grep B200DDP_ > $O/r2_tuned_env_n$N.txt
 timeout 400 $TR --master-port 29553 bench.py --gpus $N --steps 30 --warmup 5 > $O/r2_bench_n${N}_tuned.json 2> $O/r2_bench_n${N}_tuned.err
 echo "bench r18 tuned rc=$?"; cut -c1-400 $O/r2_bench_n${N}_tuned.json
+# on the 8-GPU box only the 8-rank tests run (8 GPUs cost 8x; the 2-, 3- and 4-rank tests run on smaller boxes)
+if [ "$N" = "8" ]; then
+    timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -q -rA -k "eight or -8] or [8" > $O/r2_pytest_multi_n$N.log 2>&1
+else
+    timeout 900 python -m pytest tests/test_gpu_multi.py -m gpu -q -rA > $O/r2_pytest_multi_n$N.log 2>&1
+fi
+echo "pytest rc=$?"; tail -3 $O/r2_pytest_multi_n$N.log | cut -c1-200
 timeout 400 $TR --master-port 29554 bench.py --gpus $N --model resnet50 --steps 20 --warmup 5 > $O/r2_bench_r50_n${N}.json 2> $O/r2_bench_r50_n${N}.err
 echo "bench r50 rc=$?"; cut -c1-300 $O/r2_bench_r50_n${N}.json
 unset B200DDP_NVLS_DEPTH B200DDP_P2P_BLOCKS B200DDP_NVLS_BLOCKS
 timeout 200 $TR --master-port 29556 bench.py --gpus $N --model task4 --steps 30 --warmup 5 > $O/r2_bench_task4_n${N}.json 2> $O/r2_bench_task4_n${N}.err
 echo "bench task4 rc=$?"; cut -c1-300 $O/r2_bench_task4_n${N}.json
 timeout 200 $TR --master-port 29557 tools/bcast_bench.py --model resnet50 --out $O/r2_bcast_n$N.json 2>&1 | tail -1
+timeout 300 $TR --master-port 29552 tools/sweep_allreduce.py --min-log2 12 --max-log2 30 --step-log2 3 --dtypes fp32,bf16 \
+    --out $O/r2_sweep_n${N}_pow4.jsonl > $O/r2_sweep_n${N}_pow4.log 2>&1
+echo "sweep pow4 rc=$?"
 timeout 200 $TR --master-port 29558 tools/step_timeline.py --overlap off --out $O/r2_timeline_n${N}_off.json 2>&1 | tail -1
