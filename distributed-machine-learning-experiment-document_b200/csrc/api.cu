@@ -635,25 +635,29 @@ int b200ddp_allreduce_pick(const b200ddp_ctx *ctx, int64_t nelem, int dtype) {
     if (ctx->world == 1) return B200DDP_ALGO_ONESHOT;
     const size_t bytes = (size_t)nelem * dtype_size(dtype);
     if (!ctx->peers_ready) return ctx->nccl_comm ? (int)B200DDP_ALGO_NCCL : (int)B200DDP_ESTATE;
-    // Crossovers measured on 2 and 8 B200s (profiles/r01_sweep_*.jsonl).  One-shot moves (N-1) x S
-    // per GPU and only pays off while the bucket is so small that saving the separate update
-    // launch (fused one-shot + SGD) matters; two-shot moves 2 (N-1)/N x S and beats NCCL up to
-    // ~128 MB (579 vs 419 GB/s busbw at 64 MB, 8 GPUs); above that NCCL's in-switch (NVLS)
-    // reduction wins (727 vs 646 GB/s at 1 GiB).
+    // Crossovers measured on 2, 4 and 8 B200s in round 2 (profiles/r02_sweep_n{2,4,8}_fp32_variants.jsonl,
+    // r02_sweep_n{4,8}_fp32_bf16.jsonl).  One-shot moves (N-1) x S per GPU and only pays off while the
+    // bucket is so small that saving the separate update launch (fused one-shot + SGD) matters: at 1 MB
+    // two-shot already wins on 8 GPUs (20.7 vs 29.7 us) and on 4 (19.7 vs 22.0 us).  Two-shot moves
+    // 2 (N-1)/N x S and beats NCCL at every size up to 256 MB on 2 and 4 GPUs (117 vs 139 us at the
+    // ResNet-18 bucket on 4 GPUs) and up to 64 MB on 8.
     const long long oneshot_max = ctx->oneshot_max_bytes != -2
                                       ? ctx->oneshot_max_bytes
                                       : (long long)(ctx->world <= 2 ? 1024 : ctx->world <= 4 ? 512 : 256) << 10;
     if ((long long)bytes <= oneshot_max) return B200DDP_ALGO_ONESHOT;
-    // In-switch reduction, when a multicast mapping was adopted.  Measured on 8 GPUs
-    // (profiles/r01_sweep_n8_nvls_*.jsonl): level with two-shot up to 16 MB, then ahead - 574 vs
-    // 551 GB/s at 64 MB, 768 vs 620 (NCCL 657) at 256 MB, 791 vs 641 (NCCL 720) at 1 GiB.  On 2
-    // GPUs it loses (380 vs 626 GB/s at 256 MB): the switch has nothing to save there.
-    // B200DDP_OPT_NVLS_MIN_BYTES overrides the threshold (-1: never).
+    // In-switch reduction, when a multicast mapping was adopted.  With the round-2 kernel (one multimem
+    // load in flight per thread, 74 blocks) on 8 GPUs: behind two-shot at 4 MB (31.7 vs 29.0 us), ahead from
+    // 16 MB (59.7 vs 62.1 us), 121.9 vs 146.1 us (642 vs 536 GB/s busbw) at the ResNet-18 bucket, 816 vs 635
+    // GB/s at 256 MB, 841 GB/s at 1 GiB (NCCL 726).  On 4 GPUs it draws level at 44 MB (119.4 vs 117.2 us) and
+    // leads from 256 MB (606 vs 623 us); on 2 GPUs it loses everywhere (134 vs 83 us): the switch has nothing
+    // to save there.  B200DDP_OPT_NVLS_MIN_BYTES overrides the threshold (-1: never).
     if (ctx->mc_ptr) {
-        const long long nvls_min = ctx->nvls_min_bytes != -2 ? ctx->nvls_min_bytes : (ctx->world >= 8 ? (24ll << 20) : -1);
+        const long long dflt = ctx->world >= 8 ? (12ll << 20) : ctx->world >= 4 ? (128ll << 20) : -1;
+        const long long nvls_min = ctx->nvls_min_bytes != -2 ? ctx->nvls_min_bytes : dflt;
         if (nvls_min >= 0 && (long long)bytes >= nvls_min) return B200DDP_ALGO_NVLS;
     }
-    // NCCL only for fp32: ncclAllReduce on bf16 rounds at every step, the kernels here once
+    // NCCL only for fp32 (ncclAllReduce on bf16 rounds at every step, the kernels here once) and only
+    // where it was measured ahead: 8 GPUs without a multicast mapping, above 128 MB (716 vs 740 us at 256 MB).
     if (ctx->world > 4 && ctx->nccl_comm && dtype == B200DDP_F32 && bytes > ((size_t)128 << 20)) return B200DDP_ALGO_NCCL;
     return B200DDP_ALGO_TWOSHOT;
 }

@@ -288,13 +288,15 @@ template <> struct Multimem<__nv_bfloat16> {
     }
 };
 
-// The reduce phase loads the links outbound (every GPU feeds S to the switch) and the broadcast
-// phase loads them inbound (every GPU receives S); they only overlap if loads and stores are in
-// flight together.  Round 1's kernel issued 4 loads, then 4 stores, per thread, and at the bucket
-// sizes of the lab's models (5.6 MB per rank) that was ONE pass: all loads of all GPUs, then all
-// stores - the two directions used one after the other.  Here every thread keeps a ring of D
-// loads in flight and, slot by slot, stores a result and immediately issues the load that reuses
-// the slot, so from the second vector on both directions are busy.
+// Every thread keeps a ring of D loads in flight and, slot by slot, stores a result and at once
+// issues the load that reuses the slot, so reduce traffic (outbound: every GPU feeds S to the
+// switch) and broadcast traffic (inbound: every GPU receives S) share the links instead of taking
+// turns.  What the round-2 sweeps on 2, 4 and 8 GPUs say about D and the grid
+// (profiles/r02_sweep_n*_fp32_variants.jsonl, with per-phase time stamps): LESS is faster.  Round 1
+// ran D = 4 on 296 blocks: 146.9 us for the 44.7 MB ResNet-18 bucket on 8 GPUs; D = 1 on 74 blocks:
+// 121.6 us (37 blocks: 119.4), data phase 105 us = 430 GB/s per GPU through the switch, which is
+// also where NCCL's own NVLS path levels off at 1 GiB.  More requests in flight only queue in the
+// switch, and their barriers (one flag word per block per peer) get dearer.
 template <typename BT, int D>
 __global__ void __launch_bounds__(kP2PThreads) nvls_kernel(P2PArgs a, char *mc) {
     const int rank = a.rank, world = a.world, bid = blockIdx.x;
