@@ -256,19 +256,17 @@ sampler_cluster_kernel(uint32_t *draws, uint32_t *resv, int32_t *perm, uint32_t 
         cluster.sync();
         if (round > 1 && *reinterpret_cast<volatile unsigned int *>(pend0 + ((round - 1) & 3)) == 0u) break;
         if (cta == 0 && tid == 0) pend[(round + 1) & 3] = 0u;   // the slot the NEXT round will count into
-        // all of this thread's loads in flight together - the two reservation words AND, speculatively,
-        // the two permutation entries it will swap if it wins - then all of its swaps: ONE L2 round trip
-        // per round before the stores instead of two dependent ones (a winner holds both positions, so
-        // nobody else writes them this round and the early read is the value the late read would see).
+        // all of this thread's checks in flight together, then all of its swaps: two L2 round trips
+        // per round instead of two per iterate.  Measured dead end (round 2): also reading the two
+        // permutation entries speculatively with the reservation words (one round trip less for
+        // winners) is SLOWER - 218 vs 195 us at n = 60,000: every pending iterate then makes four
+        // random L2 reads per round instead of two, and most iterates lose most rounds.
         uint32_t ri[kClusterIters], rt[kClusterIters];
-        int32_t pa[kClusterIters], pb[kClusterIters];
 #pragma unroll
         for (int k = 0; k < kClusterIters; ++k)
             if (mask & (1u << k)) {
                 ri[k] = __ldcg(resv + gtid + k * nthreads);
                 rt[k] = __ldcg(resv + tg[k]);
-                pa[k] = __ldcg(perm + gtid + k * nthreads);
-                pb[k] = __ldcg(perm + tg[k]);
             }
         unsigned int win = 0;
 #pragma unroll
@@ -276,6 +274,13 @@ sampler_cluster_kernel(uint32_t *draws, uint32_t *resv, int32_t *perm, uint32_t 
             if (mask & (1u << k)) {
                 const uint32_t key = (round << 16) | (0xffffu - (gtid + k * nthreads));
                 if (ri[k] == key && rt[k] == key) win |= 1u << k;
+            }
+        int32_t pa[kClusterIters], pb[kClusterIters];
+#pragma unroll
+        for (int k = 0; k < kClusterIters; ++k)
+            if ((win & (1u << k)) && tg[k] != gtid + k * nthreads) {
+                pa[k] = __ldcg(perm + gtid + k * nthreads);
+                pb[k] = __ldcg(perm + tg[k]);
             }
 #pragma unroll
         for (int k = 0; k < kClusterIters; ++k)
