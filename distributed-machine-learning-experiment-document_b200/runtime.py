@@ -119,18 +119,26 @@ class Context:
             check(_lib.lib().b200ddp_ipc_open_peers(self.handle, blob), "ipc_open_peers")
             self.has_peers = True
             self._ipc = True
-        if nccl and not self.has_nccl:
-            uid = ctypes.create_string_buffer(_lib.NCCL_UID_BYTES)
-            if self.rank == 0:
-                check(_lib.lib().b200ddp_nccl_unique_id(uid), "nccl_unique_id")
-            box = [bytes(uid.raw)]
-            dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
-            uid = ctypes.create_string_buffer(box[0], _lib.NCCL_UID_BYTES)
-            check(_lib.lib().b200ddp_nccl_init(self.handle, uid), "nccl_init")
-            self.has_nccl = True
+        mode = os.environ.get("B200DDP_NCCL", "1")      # "1": join now; "lazy": on first use of the NCCL algorithm; "0": never
+        if nccl and mode == "1":
+            self._connect_nccl()
         if p2p and os.environ.get("B200DDP_SYMMETRIC", "1") != "0":
             self._adopt_symmetric(group)
         return self
+
+    def _connect_nccl(self):
+        """Join the library's own NCCL communicator (collective over the context's group)."""
+        if self.has_nccl or self.world == 1:
+            return
+        group = self._group
+        uid = ctypes.create_string_buffer(_lib.NCCL_UID_BYTES)
+        if self.rank == 0:
+            check(_lib.lib().b200ddp_nccl_unique_id(uid), "nccl_unique_id")
+        box = [bytes(uid.raw)]
+        dist.broadcast_object_list(box, src=dist.get_global_rank(group, 0) if group is not None else 0, group=group)
+        uid = ctypes.create_string_buffer(box[0], _lib.NCCL_UID_BYTES)
+        check(_lib.lib().b200ddp_nccl_init(self.handle, uid), "nccl_init")
+        self.has_nccl = True
 
     def _adopt_symmetric(self, group):
         """Move the staging area into torch symmetric memory, which also yields a multicast
@@ -262,6 +270,8 @@ class Context:
         """Returns the staging offset (bytes) at which the sums are."""
         res = c_size_t()
         a = _lib.ALGO_NAMES[algo] if isinstance(algo, str) else int(algo)
+        if a == _lib.ALGO_NCCL and not self.has_nccl and os.environ.get("B200DDP_NCCL", "1") == "lazy":
+            self._connect_nccl()            # every rank asks for the NCCL algorithm at the same call: collective
         check(_lib.lib().b200ddp_allreduce(self.handle, int(offset_bytes), int(nelem), dtype_code(dtype), a,
                                            _stream_handle(stream), byref(res)), "allreduce")
         return int(res.value)
