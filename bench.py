@@ -467,7 +467,7 @@ def parity_check(torch, dist, b200ddp, numels, world, rank, dev, bucket_dtype):
     ctx = b200ddp.default_context()
     GradSync = b200ddp.GradSync
     pow2 = world & (world - 1) == 0
-    algos = ["twoshot", "oneshot"] + (["nvls"] if ctx.has_multicast else []) + (["nccl"] if ctx.has_nccl else [])
+    algos = ["twoshot", "oneshot"] + (["nvls"] if ctx.has_multicast else []) + (["nccl"] if b200ddp.runtime.nccl_mode() != "0" else [])
     only = os.environ.get("B200DDP_PARITY_ONLY")            # bisecting aid: comma list of case names
     skip_dense = os.environ.get("B200DDP_PARITY_SKIP_DENSE") == "1"
     report = {"algos": {}, "world": world, "tensors": len(numels), "elements": int(sum(numels)),

@@ -32,6 +32,12 @@ def dtype_code(d) -> int:
         raise ValueError(f"bucket dtype must be fp32 or bf16, got {d!r}") from None
 
 
+def nccl_mode() -> str:
+    """B200DDP_NCCL: "lazy" (default), "1" (join at connect), "0" (never)."""
+    m = os.environ.get("B200DDP_NCCL", "lazy")
+    return m if m in ("lazy", "1", "0") else "lazy"
+
+
 def _require_cuda():
     if not torch.cuda.is_available():
         raise B200DDPError("b200ddp needs a CUDA device (sm_100a); there is no CPU fallback")
@@ -119,8 +125,13 @@ class Context:
             check(_lib.lib().b200ddp_ipc_open_peers(self.handle, blob), "ipc_open_peers")
             self.has_peers = True
             self._ipc = True
-        mode = os.environ.get("B200DDP_NCCL", "1")      # "1": join now; "lazy": on first use of the NCCL algorithm; "0": never
-        if nccl and mode == "1":
+        # The library's own NCCL communicator is joined on first use of the NCCL algorithm, not here:
+        # measured on 8 x B200 (profiles/r02_second_nccl_comm_n8.md), a SECOND NVLS-capable communicator in
+        # the process (torch's process group holds the first) puts ~0.35 us of idle time between consecutive
+        # kernels of every later CUDA-graph replay - 125 us on the 320 kernels of a ResNet-18 step.
+        # B200DDP_NCCL=1 joins now (then AUTO may pick NCCL for fp32 buckets above 128 MB on more than
+        # 4 GPUs without a multicast mapping); B200DDP_NCCL=0 never joins.
+        if nccl and nccl_mode() == "1":
             self._connect_nccl()
         if p2p and os.environ.get("B200DDP_SYMMETRIC", "1") != "0":
             self._adopt_symmetric(group)
@@ -270,7 +281,7 @@ class Context:
         """Returns the staging offset (bytes) at which the sums are."""
         res = c_size_t()
         a = _lib.ALGO_NAMES[algo] if isinstance(algo, str) else int(algo)
-        if a == _lib.ALGO_NCCL and not self.has_nccl and os.environ.get("B200DDP_NCCL", "1") == "lazy":
+        if a == _lib.ALGO_NCCL and not self.has_nccl and nccl_mode() == "lazy":
             self._connect_nccl()            # every rank asks for the NCCL algorithm at the same call: collective
         check(_lib.lib().b200ddp_allreduce(self.handle, int(offset_bytes), int(nelem), dtype_code(dtype), a,
                                            _stream_handle(stream), byref(res)), "allreduce")
