@@ -63,3 +63,39 @@ def test_both_arms_spell_the_workload_identically():
     cfg = bench.workload_config("resnet18", 128, 4)
     assert cfg["params"] == 11181642 and cfg["tensors"] == 62 and cfg["global_batch"] == 512
     assert "model" not in cfg and "workload" in cfg
+
+
+def test_parity_check_inputs_have_an_exactly_computable_mean():
+    """bench.parity_check compares the multi-GPU result BIT FOR BIT with a mean every rank computes
+    locally; that only works if the synthetic gradients sum exactly in fp32 in any order."""
+    import itertools
+    import torch
+    import bench
+    numels = [1, 33, 4099]
+    world = 8
+    per_rank = [bench._exact_grads(torch, numels, r, 3, "cpu")[0] for r in range(world)]
+    ints = [bench._exact_grads(torch, numels, r, 3, "cpu")[1] for r in range(world)]
+    for t in range(len(numels)):
+        want = (sum(ints[r][t] for r in range(world)).to(torch.float64) * 2.0 ** -20 / world)
+        assert all(int(v.abs().max()) <= 4096 for v in (ints[r][t] for r in range(world)))
+        for order in (range(world), reversed(range(world)), [3, 7, 0, 5, 1, 6, 2, 4]):
+            acc = torch.zeros(numels[t])
+            for r in order:
+                acc = acc + per_rank[r][t]
+            assert torch.equal((acc / world).to(torch.float64), want)          # exact, whatever the order
+        # pre-scaling by 1/N in the pack (what power-of-two worlds do) gives the same bits
+        acc = torch.zeros(numels[t])
+        for r in range(world):
+            acc = acc + per_rank[r][t] * (1.0 / world)
+        assert torch.equal(acc.to(torch.float64), want)
+    assert not torch.equal(per_rank[0][2], per_rank[1][2])                     # ranks really differ
+
+
+def test_nccl_mode_parsing(monkeypatch):
+    import b200ddp
+    for value, want in ((None, "lazy"), ("1", "1"), ("0", "0"), ("lazy", "lazy"), ("nonsense", "lazy")):
+        if value is None:
+            monkeypatch.delenv("B200DDP_NCCL", raising=False)
+        else:
+            monkeypatch.setenv("B200DDP_NCCL", value)
+        assert b200ddp.runtime.nccl_mode() == want
