@@ -87,7 +87,11 @@ int b200ddp_flags(b200ddp_ctx *ctx, void **ptr);
  * rank 0 packs, the others unpack straight out of rank 0's memory over NVLink. */
 int b200ddp_peer_staging(b200ddp_ctx *ctx, int peer, void **ptr);
 
-/* NCCL baseline collective: rank 0 makes the id, every rank joins (collective). */
+/* NCCL baseline collective: rank 0 makes the id, every rank joins (collective).
+ * Join it only when B200DDP_ALGO_NCCL is really wanted: measured on 8 x B200, a second NVLS-capable
+ * communicator in a process that already holds one (torch.distributed's) puts ~0.3 us of idle time
+ * between consecutive kernels of every later CUDA-graph replay (profiles/r02_second_nccl_comm_n8.md).
+ * The Python side therefore joins on the first all-reduce that asks for the algorithm (B200DDP_NCCL=lazy). */
 int b200ddp_nccl_unique_id(void *out_uid /* B200DDP_NCCL_UID_BYTES */);
 int b200ddp_nccl_init(b200ddp_ctx *ctx, const void *uid);
 
