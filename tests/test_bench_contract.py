@@ -99,3 +99,11 @@ def test_nccl_mode_parsing(monkeypatch):
         else:
             monkeypatch.setenv("B200DDP_NCCL", value)
         assert b200ddp.runtime.nccl_mode() == want
+
+
+def test_reference_arm_task4_runs_replicas_of_the_whole_model():
+    """configs[3] on the host cores: N GPUs = N / 2 replicas, so the CPU counterpart is N / 2 gloo ranks of
+    the whole lab CNN with plain SGD (codes/task4/model.py:126)."""
+    d = json.loads(_run(None, "--gpus", "4", "--model", "task4").strip())       # the later --model wins over _run's
+    assert d["impl"] == "reference" and d["n_gpus"] == 4 and "gloo x2" in d["arm"]["where"]
+    assert d["config"]["parallelism"] == "dp2" and "task4" in d["config"]["workload"] and d["value"] > 0
